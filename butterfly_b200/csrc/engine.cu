@@ -1,0 +1,534 @@
+// Engine: owns device memory (weights, paged KV cache, workspaces), runs the partitioned block
+// forward for prefill and decode on one CUDA stream, captures the decode step in a CUDA graph and
+// calls NCCL for the row-parallel all-reduce / vocabulary all-gather (tp > 1).
+// Realises the reference's intended "Distributed Inference Engine" (ref:CLAUDE.md:19), which has
+// no implementation to follow; the structure is SURVEY.md section 3 (call stacks 3 and 4).
+#include "engine.h"
+
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace bfly {
+
+unsigned long long g_launch_count = 0;
+
+// ---- NCCL, resolved at run time so the library loads (and exports its ABI) without NCCL/GPU ----
+namespace {
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl() {
+  if (g_nccl.lib) return BFLY_OK;
+  void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);   // the copy torch already loaded, if any
+  if (!lib) {
+    set_error(std::string("cannot load libnccl.so.2: ") + dlerror());
+    return BFLY_ENCCL;
+  }
+  g_nccl.GetUniqueId = (int (*)(void*))dlsym(lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(void**, int, NcclId, int))dlsym(lib, "ncclCommInitRank");
+  g_nccl.CommDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
+  g_nccl.AllGather = (int (*)(const void*, void*, size_t, int, void*, cudaStream_t))dlsym(lib, "ncclAllGather");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllReduce || !g_nccl.AllGather) {
+    set_error("libnccl.so.2 lacks a required symbol");
+    return BFLY_ENCCL;
+  }
+  g_nccl.lib = lib;
+  return BFLY_OK;
+}
+
+// ncclDataType_t / ncclRedOp_t values (nccl.h): ncclInt8 = 0, ncclFloat32 = 7, ncclSum = 0
+constexpr int kNcclInt8 = 0, kNcclFloat = 7, kNcclSum = 0;
+
+#define BFLY_NCCL(expr)                                                                          \
+  do {                                                                                           \
+    int _r = (expr);                                                                             \
+    if (_r != 0) {                                                                               \
+      set_error(std::string(#expr) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(_r) : "nccl error")); \
+      return BFLY_ENCCL;                                                                         \
+    }                                                                                            \
+  } while (0)
+
+template <typename T>
+int dev_alloc(Engine* e, T** p, size_t count, uint64_t* account) {
+  void* q = nullptr;
+  const size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+  cudaError_t err = cudaMalloc(&q, bytes);
+  if (err != cudaSuccess) {
+    set_error("cudaMalloc of " + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(err));
+    return BFLY_ENOMEM;
+  }
+  e->allocations.push_back(q);
+  if (account) *account += bytes;
+  *p = (T*)q;
+  return BFLY_OK;
+}
+}  // namespace
+
+int nccl_unique_id(void* out128) {
+  BFLY_TRY(load_nccl());
+  BFLY_NCCL(g_nccl.GetUniqueId(out128));
+  return BFLY_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
+  const bfly_model_desc& c = desc;
+  BFLY_CHECK(c.family >= 0 && c.family <= 2, "family");
+  BFLY_CHECK(c.hidden > 0 && c.hidden % 8 == 0, "hidden % 8 == 0");
+  BFLY_CHECK(c.head_dim == 32 || c.head_dim == 64 || c.head_dim == 128, "head_dim in {32,64,128}");
+  BFLY_CHECK(c.tp >= 1 && c.rank >= 0 && c.rank < c.tp, "0 <= rank < tp");
+  BFLY_CHECK(c.n_heads % c.tp == 0 && c.n_kv_heads % c.tp == 0 && c.n_heads % c.n_kv_heads == 0, "heads vs tp");
+  BFLY_CHECK(c.n_experts == 0 ? c.ffn % c.tp == 0 : (c.n_experts % c.tp == 0 && c.n_experts <= 32), "ffn/experts vs tp");
+  BFLY_CHECK(c.n_experts == 0 || (c.top_k >= 1 && c.top_k <= c.n_experts), "top_k");
+  BFLY_CHECK(c.page_size >= 8 && (c.page_size & (c.page_size - 1)) == 0, "page_size power of two >= 8");
+  BFLY_CHECK(c.max_batch >= 1 && c.max_ctx >= 1 && c.max_tokens >= c.max_batch, "max_batch/max_ctx/max_tokens");
+  BFLY_CHECK(c.rope_theta > 0.f || c.max_pos >= c.max_ctx, "learned positions need max_pos >= max_ctx");
+  BFLY_CUDA(cudaSetDevice(device));
+  BFLY_TRY(gemm_init());
+
+  Engine* e = new Engine();
+  e->d = c;
+  e->device = device;
+  cudaDeviceProp prop;
+  BFLY_CUDA(cudaGetDeviceProperties(&prop, device));
+  e->sm_count = prop.multiProcessorCount;
+  BFLY_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+
+  e->q_local = c.n_heads / c.tp;
+  e->kv_local = c.n_kv_heads / c.tp;
+  e->qkv_rows = (e->q_local + 2 * e->kv_local) * c.head_dim;
+  e->experts_local = c.n_experts ? c.n_experts / c.tp : 0;
+  e->n_blocks = c.n_experts ? e->experts_local : 1;
+  e->f_block = c.n_experts ? c.ffn : c.ffn / c.tp;
+  e->gated = c.family != BFLY_FAMILY_GPT2;
+  e->ffn_in_rows = e->n_blocks * e->f_block * (e->gated ? 2 : 1);
+  e->ffn_act_cols = e->n_blocks * e->f_block;
+  e->v_shard = (c.vocab + c.tp - 1) / c.tp;
+  e->v0 = std::min(c.vocab, c.rank * e->v_shard);
+  e->v_local = std::min(c.vocab, (c.rank + 1) * e->v_shard) - e->v0;
+  e->pages_per_seq = (c.max_ctx + c.page_size - 1) / c.page_size;
+  e->n_pages = (int64_t)c.max_batch * e->pages_per_seq;
+  e->layer_kv_elems = e->n_pages * 2 * e->kv_local * c.page_size * c.head_dim;
+  e->layers.resize(c.n_layers);
+
+  const int h = c.hidden, maxT = c.max_tokens, maxB = c.max_batch;
+  // split-K scratch: worst case over every GEMM shape and every token count a forward can see
+  const int gemm_m[5] = {e->qkv_rows, h, e->ffn_in_rows, h, std::max(e->v_local, 1)};
+  const int gemm_k[5] = {h, e->q_local * c.head_dim, h, e->ffn_act_cols, h};
+  size_t ws = 0;
+  for (int g = 0; g < 5; ++g) {
+    const int n_cap = (g == 4) ? maxB : maxT;
+    for (int n = 1; n <= n_cap; n = (n < 16 ? n + 1 : n + 16)) {
+      const GemmPlan p = gemm_plan(gemm_m[g], n, gemm_k[g], e->sm_count, kMaxSplits);
+      ws = std::max(ws, (size_t)p.splits * n * gemm_m[g]);
+    }
+    const GemmPlan p = gemm_plan(gemm_m[g], n_cap, gemm_k[g], e->sm_count, kMaxSplits);
+    ws = std::max(ws, (size_t)p.splits * n_cap * gemm_m[g]);
+  }
+  e->ws_elems = ws + 64;
+  size_t po = 0, pml = 0;
+  for (int t = 1; t <= maxT; t = (t < 64 ? t + 1 : t + 64)) {
+    const int s = attn_decode_splits(t, e->kv_local, c.max_ctx, e->sm_count);
+    po = std::max(po, (size_t)t * e->q_local * s * c.head_dim);
+    pml = std::max(pml, (size_t)t * e->q_local * s * 2);
+  }
+  {
+    const int s = attn_decode_splits(maxT, e->kv_local, c.max_ctx, e->sm_count);
+    po = std::max(po, (size_t)maxT * e->q_local * s * c.head_dim);
+    pml = std::max(pml, (size_t)maxT * e->q_local * s * 2);
+  }
+
+  int rc = BFLY_OK;
+  uint64_t* wsb = &e->workspace_bytes;
+  auto A = [&](int r) { if (rc == BFLY_OK) rc = r; };
+  A(dev_alloc(e, &e->kv_pages, (size_t)c.n_layers * e->layer_kv_elems, &e->kv_bytes));
+  A(dev_alloc(e, &e->page_table, (size_t)e->n_pages, wsb));
+  A(dev_alloc(e, &e->seq_lens, (size_t)maxB, wsb));
+  A(dev_alloc(e, &e->step_counter, 1, wsb));
+  A(dev_alloc(e, &e->residual, (size_t)maxT * h, wsb));
+  A(dev_alloc(e, &e->xn, (size_t)maxT * h, wsb));
+  A(dev_alloc(e, &e->q, (size_t)maxT * e->q_local * c.head_dim, wsb));
+  A(dev_alloc(e, &e->attn_out, (size_t)maxT * e->q_local * c.head_dim, wsb));
+  A(dev_alloc(e, &e->act, (size_t)maxT * e->ffn_act_cols, wsb));
+  A(dev_alloc(e, &e->ws, e->ws_elems, wsb));
+  A(dev_alloc(e, &e->part_o, po, wsb));
+  A(dev_alloc(e, &e->part_ml, pml, wsb));
+  if (c.tp > 1) A(dev_alloc(e, &e->red, (size_t)maxT * h, wsb));
+  if (c.n_experts) A(dev_alloc(e, &e->route_w, (size_t)maxT * e->experts_local, wsb));
+  A(dev_alloc(e, &e->logits, (size_t)maxB * e->v_shard, wsb));
+  if (c.tp > 1) A(dev_alloc(e, &e->logits_all, (size_t)c.tp * maxB * e->v_shard, wsb));
+  A(dev_alloc(e, &e->keys, (size_t)maxB, wsb));
+  A(dev_alloc(e, &e->keys_all, (size_t)c.tp * maxB, wsb));
+  A(dev_alloc(e, &e->tokens_in, (size_t)maxT, wsb));
+  A(dev_alloc(e, &e->cur_tokens, (size_t)maxB, wsb));
+  A(dev_alloc(e, &e->history, (size_t)kMaxGreedySteps * maxB, wsb));
+  if (c.rope_theta > 0.f) A(dev_alloc(e, &e->rope_table, (size_t)c.max_ctx * (c.head_dim / 2), wsb));
+  if (rc != BFLY_OK) { delete e; return rc; }
+
+  // identity page table, zero lengths
+  std::vector<int> table((size_t)e->n_pages);
+  for (int64_t i = 0; i < e->n_pages; ++i) table[(size_t)i] = (int)i;
+  BFLY_CUDA(cudaMemcpy(e->page_table, table.data(), table.size() * sizeof(int), cudaMemcpyHostToDevice));
+  BFLY_CUDA(cudaMemset(e->seq_lens, 0, (size_t)maxB * sizeof(int)));
+  BFLY_CUDA(cudaMemset(e->step_counter, 0, sizeof(int)));
+  BFLY_CUDA(cudaMemset(e->cur_tokens, 0, (size_t)maxB * sizeof(int)));
+  if (c.rope_theta > 0.f) {
+    // cos/sin in double, as the oracle does (oracle/ops.py::rope), stored fp32
+    const int half = c.head_dim / 2;
+    std::vector<float2> tab((size_t)c.max_ctx * half);
+    for (int i = 0; i < half; ++i) {
+      const double inv = std::pow((double)c.rope_theta, -2.0 * i / (double)c.head_dim);
+      for (int p = 0; p < c.max_ctx; ++p) {
+        const double a = (double)p * inv;
+        tab[(size_t)p * half + i] = make_float2((float)std::cos(a), (float)std::sin(a));
+      }
+    }
+    BFLY_CUDA(cudaMemcpy(e->rope_table, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  }
+  BFLY_CUDA(cudaHostAlloc((void**)&e->pinned, kPinnedBytes, cudaHostAllocDefault));
+  *out = e;
+  return BFLY_OK;
+}
+
+Engine::~Engine() {
+  for (auto& kv : graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
+  for (void* p : allocations) cudaFree(p);
+  if (pinned) cudaFreeHost(pinned);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+// ---- weights -----------------------------------------------------------------------------------
+int Engine::alloc_weight(const std::string& name, int64_t rows, int64_t cols) {
+  BFLY_CHECK(rows > 0 && cols > 0, "weight shape");
+  BFLY_CUDA(cudaSetDevice(device));
+  auto it = weights.find(name);
+  if (it != weights.end()) {
+    BFLY_CHECK(it->second.rows == rows && it->second.cols == cols, "weight re-registered with another shape: " + name);
+    return BFLY_OK;
+  }
+  DevTensor t{};
+  t.rows = rows; t.cols = cols;
+  BFLY_TRY(dev_alloc(this, &t.ptr, (size_t)(rows * cols), &weight_bytes));
+  weights[name] = t;
+  ready = false;
+  return BFLY_OK;
+}
+
+int Engine::upload_weight(const std::string& name, const void* host, int64_t rows, int64_t cols) {
+  BFLY_TRY(alloc_weight(name, rows, cols));
+  BFLY_CUDA(cudaMemcpy(weights[name].ptr, host, (size_t)(rows * cols) * sizeof(bf16), cudaMemcpyHostToDevice));
+  return BFLY_OK;
+}
+
+int Engine::fill_weight_block(const std::string& name, int64_t dst_row, int64_t dst_col, uint64_t key,
+                              int64_t ncols_full, int64_t r0, int64_t c0, int64_t rows, int64_t cols, float scale,
+                              float offset) {
+  auto it = weights.find(name);
+  if (it == weights.end()) { set_error("unknown weight: " + name); return BFLY_ESTATE; }
+  const DevTensor& t = it->second;
+  BFLY_CHECK(dst_row >= 0 && dst_col >= 0 && dst_row + rows <= t.rows && dst_col + cols <= t.cols,
+             "fill_weight_block: block outside " + name);
+  BFLY_CUDA(cudaSetDevice(device));
+  return launch_fill_synth(t.ptr + dst_row * t.cols + dst_col, t.cols, key, ncols_full, r0, c0, rows, cols, scale,
+                           offset, stream);
+}
+
+int Engine::read_weight(const std::string& name, void* host, int64_t max_bytes) {
+  auto it = weights.find(name);
+  if (it == weights.end()) { set_error("unknown weight: " + name); return BFLY_ESTATE; }
+  const int64_t bytes = it->second.rows * it->second.cols * (int64_t)sizeof(bf16);
+  BFLY_CHECK(max_bytes >= bytes, "read_weight: buffer too small");
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  BFLY_CUDA(cudaMemcpy(host, it->second.ptr, (size_t)bytes, cudaMemcpyDeviceToHost));
+  return BFLY_OK;
+}
+
+int Engine::find(const std::string& name, int64_t rows, int64_t cols, bool required, bf16** out) {
+  auto it = weights.find(name);
+  if (it == weights.end()) {
+    *out = nullptr;
+    if (!required) return BFLY_OK;
+    set_error("missing weight: " + name);
+    return BFLY_ESTATE;
+  }
+  if (it->second.rows != rows || it->second.cols != cols) {
+    set_error("weight " + name + " has shape [" + std::to_string(it->second.rows) + "," + std::to_string(it->second.cols) +
+              "], expected [" + std::to_string(rows) + "," + std::to_string(cols) + "]");
+    return BFLY_EINVAL;
+  }
+  *out = it->second.ptr;
+  return BFLY_OK;
+}
+
+int Engine::weights_ready() {
+  const bfly_model_desc& c = d;
+  const int h = c.hidden;
+  const bool ln = c.family == BFLY_FAMILY_GPT2;
+  BFLY_TRY(find("embed", c.vocab, h, true, &embed));
+  BFLY_TRY(find("pos_embed", c.max_pos, h, c.rope_theta == 0.f, &pos_embed));
+  BFLY_TRY(find("final_norm.w", h, 1, true, &final_norm_w));
+  BFLY_TRY(find("final_norm.b", h, 1, ln, &final_norm_b));
+  BFLY_TRY(find("lm_head", v_local, h, v_local > 0, &lm_head));
+  for (int l = 0; l < c.n_layers; ++l) {
+    const std::string p = "layers." + std::to_string(l) + ".";
+    LayerW& w = layers[l];
+    BFLY_TRY(find(p + "attn_norm.w", h, 1, true, &w.attn_norm_w));
+    BFLY_TRY(find(p + "attn_norm.b", h, 1, ln, &w.attn_norm_b));
+    BFLY_TRY(find(p + "ffn_norm.w", h, 1, true, &w.ffn_norm_w));
+    BFLY_TRY(find(p + "ffn_norm.b", h, 1, ln, &w.ffn_norm_b));
+    BFLY_TRY(find(p + "wqkv", qkv_rows, h, true, &w.wqkv));
+    BFLY_TRY(find(p + "bqkv", qkv_rows, 1, c.bias != 0, &w.bqkv));
+    BFLY_TRY(find(p + "wo", h, q_local * c.head_dim, true, &w.wo));
+    BFLY_TRY(find(p + "bo", h, 1, c.bias != 0, &w.bo));
+    BFLY_TRY(find(p + (gated ? "w_gate_up" : "w_up"), ffn_in_rows, h, true, &w.w_in));
+    BFLY_TRY(find(p + "b_up", ffn_act_cols, 1, c.bias != 0 && !gated, &w.b_up));
+    BFLY_TRY(find(p + "w_down", h, ffn_act_cols, true, &w.w_down));
+    BFLY_TRY(find(p + "b_down", h, 1, c.bias != 0, &w.b_down));
+    BFLY_TRY(find(p + "router", c.n_experts, h, c.n_experts > 0, &w.router));
+  }
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  ready = true;
+  return BFLY_OK;
+}
+
+// ---- communication -----------------------------------------------------------------------------
+int Engine::comm_init(const void* id128, int world, int rank) {
+  BFLY_CHECK(world == d.tp && rank == d.rank, "comm_init: world/rank must equal the plan's tp/rank");
+  if (world == 1) return BFLY_OK;
+  BFLY_TRY(load_nccl());
+  BFLY_CUDA(cudaSetDevice(device));
+  NcclId id;
+  std::memcpy(id.bytes, id128, 128);
+  BFLY_NCCL(g_nccl.CommInitRank(&comm, world, id, rank));
+  return BFLY_OK;
+}
+
+int Engine::all_reduce_f32(float* buf, size_t count) {
+  if (d.tp == 1) return BFLY_OK;
+  if (!comm) { set_error("tp > 1 but bfly_comm_init was not called"); return BFLY_ESTATE; }
+  BFLY_NCCL(g_nccl.AllReduce(buf, buf, count, kNcclFloat, kNcclSum, comm, stream));
+  return BFLY_OK;
+}
+
+int Engine::all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank) {
+  if (!comm) { set_error("tp > 1 but bfly_comm_init was not called"); return BFLY_ESTATE; }
+  BFLY_NCCL(g_nccl.AllGather(src, dst, bytes_per_rank, kNcclInt8, comm, stream));
+  return BFLY_OK;
+}
+
+// ---- forward -----------------------------------------------------------------------------------
+int Engine::gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* splits_out) {
+  const GemmPlan p = gemm_plan(M, N, K, sm_count, kMaxSplits);
+  if ((size_t)p.splits * N * M > ws_elems) { set_error("split-K scratch too small (internal sizing error)"); return BFLY_ESTATE; }
+  *splits_out = p.splits;
+  return launch_gemm(W, X, ldx, p, ws, (int64_t)N * M, nullptr, M, stream);
+}
+
+// Row-parallel output: fold slices and all-reduce when tp > 1; tells the consumer where to read.
+int Engine::row_parallel_finish(int T, int splits, const float** src, int* n_partials) {
+  const int h = d.hidden;
+  if (d.tp == 1) { *src = ws; *n_partials = splits; return BFLY_OK; }
+  BFLY_TRY(launch_reduce_partials(ws, splits, (int64_t)T * h, red, (int64_t)T * h, stream));
+  BFLY_TRY(all_reduce_f32(red, (size_t)T * h));
+  *src = red; *n_partials = 1;
+  return BFLY_OK;
+}
+
+int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_logits, bool record_history) {
+  const bfly_model_desc& c = d;
+  const int T = nb * S, h = c.hidden, dh = c.head_dim;
+  const bool ln = c.family == BFLY_FAMILY_GPT2;
+  int* lens = seq_lens + seq0;
+  const int* table = page_table + (int64_t)seq0 * pages_per_seq;
+  const int attn_splits = attn_decode_splits(T, kv_local, c.max_ctx, sm_count);
+
+  BFLY_TRY(launch_embed(tokens_dev, embed, pos_embed, lens, S, residual, T, h, c.vocab, keys, nb,
+                        record_history ? history : nullptr, step_counter, stream));
+  const float* pend_src = nullptr;
+  int pend_n = 0;
+  const bf16* pend_bias = nullptr;
+  for (int l = 0; l < c.n_layers; ++l) {
+    const LayerW& w = layers[l];
+    KvLayout kv{kv_pages + (int64_t)l * layer_kv_elems, table, pages_per_seq, c.page_size, kv_local, dh};
+    int s = 1;
+    BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, pend_bias, w.attn_norm_w, w.attn_norm_b,
+                             c.norm_eps, ln, xn, T, h, stream));
+    BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s));
+    BFLY_TRY(launch_rope_kv(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, lens, S, T, q_local, kv_local, q, kv,
+                            stream));
+    BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
+    BFLY_TRY(gemm(w.wo, attn_out, q_local * dh, h, T, q_local * dh, &s));
+    BFLY_TRY(row_parallel_finish(T, s, &pend_src, &pend_n));
+    BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, w.bo, w.ffn_norm_w, w.ffn_norm_b, c.norm_eps,
+                             ln, xn, T, h, stream));
+    if (c.n_experts)
+      BFLY_TRY(launch_moe_router(xn, w.router, T, h, c.n_experts, c.top_k, c.rank * experts_local, experts_local,
+                                 route_w, stream));
+    BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s));
+    BFLY_TRY(launch_act(ws, s, (int64_t)T * ffn_in_rows, w.b_up, gated ? ACT_SWIGLU : ACT_GELU_TANH, n_blocks, f_block,
+                        c.n_experts ? route_w : nullptr, act, T, stream));
+    BFLY_TRY(gemm(w.w_down, act, ffn_act_cols, h, T, ffn_act_cols, &s));
+    BFLY_TRY(row_parallel_finish(T, s, &pend_src, &pend_n));
+    pend_bias = w.b_down;
+  }
+  BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, pend_bias, final_norm_w, final_norm_b,
+                           c.norm_eps, ln, xn, T, h, stream));
+  // LM head on the last position of each sequence (row pitch S*h picks rows b*S + S-1)
+  int s = 1;
+  if (v_local > 0) {
+    BFLY_TRY(gemm(lm_head, xn + (int64_t)(S - 1) * h, (int64_t)S * h, v_local, nb, h, &s));
+    BFLY_TRY(launch_lm_finalize(ws, s, (int64_t)nb * v_local, nb, v_local, v0,
+                                want_logits ? logits + (int64_t)seq0 * v_shard : nullptr, v_shard, keys, stream));
+  }
+  if (c.tp > 1) {
+    BFLY_TRY(all_gather_bytes(keys, keys_all, (size_t)d.max_batch * sizeof(unsigned long long)));
+    // keys_all is [tp][max_batch]; pick over ranks with that pitch
+    BFLY_TRY(launch_pick_tokens_pitched(keys_all, c.tp, d.max_batch, nb, cur_tokens + seq0, stream));
+  } else {
+    BFLY_TRY(launch_pick_tokens_pitched(keys, 1, d.max_batch, nb, cur_tokens + seq0, stream));
+  }
+  BFLY_TRY(launch_advance(lens, nb, S, record_history ? step_counter : nullptr, stream));
+  return BFLY_OK;
+}
+
+int Engine::check_ready(int B) {
+  if (!ready) { set_error("bfly_weights_ready() has not succeeded yet"); return BFLY_ESTATE; }
+  BFLY_CHECK(B >= 1 && B <= d.max_batch, "batch must be in [1, max_batch]");
+  BFLY_CUDA(cudaSetDevice(device));
+  return BFLY_OK;
+}
+
+int Engine::fetch_outputs(int B, float* logits_host, int32_t* next_host) {
+  const bfly_model_desc& c = d;
+  if (logits_host) {
+    if (c.tp > 1) {
+      BFLY_TRY(all_gather_bytes(logits, logits_all, (size_t)c.max_batch * v_shard * sizeof(float)));
+      for (int r = 0; r < c.tp; ++r) {
+        const int r0 = std::min(c.vocab, r * v_shard), r1 = std::min(c.vocab, (r + 1) * v_shard);
+        if (r1 > r0)
+          BFLY_CUDA(cudaMemcpy2DAsync(logits_host + r0, (size_t)c.vocab * sizeof(float),
+                                      logits_all + (size_t)r * c.max_batch * v_shard, (size_t)v_shard * sizeof(float),
+                                      (size_t)(r1 - r0) * sizeof(float), B, cudaMemcpyDeviceToHost, stream));
+      }
+    } else {
+      BFLY_CUDA(cudaMemcpy2DAsync(logits_host, (size_t)c.vocab * sizeof(float), logits, (size_t)v_shard * sizeof(float),
+                                  (size_t)c.vocab * sizeof(float), B, cudaMemcpyDeviceToHost, stream));
+    }
+  }
+  if (next_host)
+    BFLY_CUDA(cudaMemcpyAsync(next_host, cur_tokens, (size_t)B * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  return BFLY_OK;
+}
+
+int Engine::prefill(const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host) {
+  BFLY_TRY(check_ready(B));
+  BFLY_CHECK(tokens_host != nullptr && S >= 1 && S <= d.max_ctx && S <= d.max_tokens, "prefill: 1 <= S <= min(max_ctx, max_tokens)");
+  BFLY_CUDA(cudaMemsetAsync(seq_lens, 0, (size_t)B * sizeof(int), stream));
+  host_len = S;
+  const int per_chunk = std::max(1, d.max_tokens / S);
+  for (int b0 = 0; b0 < B; b0 += per_chunk) {
+    const int nb = std::min(per_chunk, B - b0);
+    BFLY_CUDA(cudaMemcpyAsync(tokens_in, tokens_host + (size_t)b0 * S, (size_t)nb * S * sizeof(int),
+                              cudaMemcpyHostToDevice, stream));
+    BFLY_TRY(forward(tokens_in, b0, nb, S, logits_host != nullptr, false));
+    // tokens_in is reused by the next chunk: the H2D copy is stream-ordered after this forward
+  }
+  return fetch_outputs(B, logits_host, next_host);
+}
+
+int Engine::decode_graph(int B, bool want_logits, GraphEntry** out) {
+  const int key = B * 2 + (want_logits ? 1 : 0);
+  auto it = graphs.find(key);
+  if (it != graphs.end()) { *out = &it->second; return BFLY_OK; }
+  GraphEntry ge{};
+  const unsigned long long before = g_launch_count;
+  cudaGraph_t graph = nullptr;
+  BFLY_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+  const int rc = forward(cur_tokens, 0, B, 1, want_logits, true);
+  const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+  ge.kernel_nodes = (int)(g_launch_count - before);
+  g_launch_count = before;                      // captured launches did not execute
+  if (rc != BFLY_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+  BFLY_CUDA(ce);
+  BFLY_CUDA(cudaGraphInstantiate(&ge.exec, graph, 0));
+  cudaGraphDestroy(graph);
+  graphs[key] = ge;
+  last_graph_nodes = ge.kernel_nodes;
+  *out = &graphs[key];
+  return BFLY_OK;
+}
+
+int Engine::decode(const int32_t* tokens_host, int B, float* logits_host, int32_t* next_host) {
+  BFLY_TRY(check_ready(B));
+  BFLY_CHECK(host_len + 1 <= d.max_ctx, "decode: KV cache is full (max_ctx reached)");
+  GraphEntry* ge = nullptr;
+  BFLY_TRY(decode_graph(B, logits_host != nullptr, &ge));
+  host_len += 1;
+  if (tokens_host)
+    BFLY_CUDA(cudaMemcpyAsync(cur_tokens, tokens_host, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, stream));
+  BFLY_CUDA(cudaMemsetAsync(step_counter, 0, sizeof(int), stream));
+  BFLY_CUDA(cudaGraphLaunch(ge->exec, stream));
+  g_launch_count += (unsigned long long)ge->kernel_nodes;
+  return fetch_outputs(B, logits_host, next_host);
+}
+
+int Engine::decode_enqueue(int B, int n_steps) {
+  BFLY_TRY(check_ready(B));
+  BFLY_CHECK(n_steps >= 1 && n_steps <= kMaxGreedySteps, "n_steps in [1, 4096]");
+  BFLY_CHECK(host_len + n_steps <= d.max_ctx, "decode: KV cache would overflow max_ctx");
+  GraphEntry* ge = nullptr;
+  BFLY_TRY(decode_graph(B, false, &ge));
+  host_len += n_steps;
+  BFLY_CUDA(cudaMemsetAsync(step_counter, 0, sizeof(int), stream));
+  for (int i = 0; i < n_steps; ++i) BFLY_CUDA(cudaGraphLaunch(ge->exec, stream));
+  g_launch_count += (unsigned long long)ge->kernel_nodes * n_steps;
+  return BFLY_OK;
+}
+
+int Engine::decode_greedy(int B, int n_steps, int32_t* tokens_out_host) {
+  BFLY_TRY(decode_enqueue(B, n_steps));
+  if (tokens_out_host) {
+    // history is [step][B]; the caller wants [B][n_steps]
+    std::vector<int> tmp((size_t)n_steps * B);
+    BFLY_CUDA(cudaMemcpyAsync(tmp.data(), history, tmp.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    BFLY_CUDA(cudaStreamSynchronize(stream));
+    for (int s = 0; s < n_steps; ++s)
+      for (int b = 0; b < B; ++b) tokens_out_host[(size_t)b * n_steps + s] = tmp[(size_t)s * B + b];
+  } else {
+    BFLY_CUDA(cudaStreamSynchronize(stream));
+  }
+  return BFLY_OK;
+}
+
+int Engine::set_page_table(const int32_t* table_host, int n_seqs, int pps) {
+  BFLY_CHECK(n_seqs >= 1 && n_seqs <= d.max_batch && pps == pages_per_seq, "set_page_table: shape");
+  std::vector<char> seen((size_t)n_pages, 0);
+  for (int64_t i = 0; i < (int64_t)n_seqs * pps; ++i) {
+    const int p = table_host[i];
+    BFLY_CHECK(p >= 0 && p < n_pages && !seen[(size_t)p], "set_page_table: page ids must be unique and in range");
+    seen[(size_t)p] = 1;
+  }
+  BFLY_CUDA(cudaSetDevice(device));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  BFLY_CUDA(cudaMemcpy(page_table, table_host, (size_t)n_seqs * pps * sizeof(int), cudaMemcpyHostToDevice));
+  return BFLY_OK;
+}
+
+}  // namespace bfly

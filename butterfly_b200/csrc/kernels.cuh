@@ -1,0 +1,74 @@
+// Host-side launchers of every kernel on the partitioned block forward (SURVEY.md section 2.5,
+// K1..K9).  All pointers are device pointers; all launches go to `stream`; nothing allocates.
+#pragma once
+
+#include "common.cuh"
+
+namespace bfly {
+
+typedef __nv_bfloat16 bf16;
+
+// Paged KV cache of ONE layer on one rank: [n_pages][2 (K,V)][kv_local][page_size][head_dim] bf16,
+// addressed through page_table[seq][logical page].
+struct KvLayout {
+  bf16* base;
+  const int* page_table;
+  int pages_per_seq;
+  int page_size;
+  int kv_local;
+  int head_dim;
+};
+
+enum ActMode : int { ACT_SWIGLU = 0, ACT_GELU_TANH = 1 };
+
+// Token t = b*S + s of a forward over S new tokens per sequence sits at position seq_lens[b] + s.
+
+// synth.cu -- weights as a pure function of (key, row, col); bit-identical to weights.synth_block
+int launch_fill_synth(bf16* dst, int64_t dst_pitch, uint64_t key, int64_t ncols_full, int64_t r0, int64_t c0,
+                      int64_t rows, int64_t cols, float scale, float offset, cudaStream_t stream);
+
+// elementwise.cu
+// Clears argmax_keys[0..n_keys) and, when `history` is given, records the tokens fed at this step at
+// history[*step_counter * T + t] (free-running greedy decode).
+int launch_embed(const int* tokens, const bf16* table, const bf16* pos_table, const int* seq_lens, int S,
+                 float* residual, int T, int h, int vocab, unsigned long long* argmax_keys, int n_keys,
+                 int* history, const int* step_counter, cudaStream_t stream);
+int launch_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
+                    const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
+                    int T, int h, cudaStream_t stream);
+int launch_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, const bf16* bias,
+                   const float2* rope_table, const int* seq_lens, int S, int T, int nq, int nk, bf16* q_out,
+                   KvLayout kv, cudaStream_t stream);
+int launch_act(const float* in, int n_partials, int64_t partial_stride, const bf16* bias, int mode,
+               int n_blocks, int f_block, const float* route_w, bf16* out, int T, cudaStream_t stream);
+int launch_lm_finalize(const float* partials, int n_partials, int64_t partial_stride, int T, int v_local,
+                       int v0, float* logits, int64_t logits_ld, unsigned long long* keys, cudaStream_t stream);
+int launch_pick_tokens_pitched(const unsigned long long* keys, int n_ranks, int pitch, int T, int* tokens_out,
+                               cudaStream_t stream);
+int launch_advance(int* seq_lens, int B, int S, int* step_counter, cudaStream_t stream);
+int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_experts, int top_k,
+                      int first_local, int n_local, float* route_w, cudaStream_t stream);
+int launch_reduce_partials(const float* partials, int n_partials, int64_t partial_stride, float* out,
+                           int64_t count, cudaStream_t stream);
+
+// attn_decode.cu -- paged-KV attention, one query token per (virtual) sequence, split over the context
+int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count);
+int launch_attn_decode(const bf16* q, KvLayout kv, const int* seq_lens, int S, int T, int nq, float* part_o,
+                       float* part_ml, int n_splits, bf16* out, cudaStream_t stream);
+
+// gemm_tcgen05.cu -- C[n][m] (+= over split-K slices) = sum_k W[m][k] * X[n][k]; W, X bf16 K-major.
+struct GemmPlan {
+  int M, N, K;          // M = weight rows (features), N = tokens
+  int bn;               // token tile (UMMA N), multiple of 16, <= 256
+  int splits;           // split-K factor; each slice is written to out + s * split_stride
+  int stages;
+  size_t smem_bytes;
+};
+int gemm_init();        // resolves cuTensorMapEncodeTiled, sets kernel attributes (once per process)
+GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits);
+// out_bf16 != nullptr requires splits == 1 (direct bf16 output); otherwise fp32 slices in out_f32.
+// ldx = row pitch of X in elements (>= K, multiple of 8).
+int launch_gemm(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& plan, float* out_f32,
+                int64_t split_stride, bf16* out_bf16, int64_t ldc, cudaStream_t stream);
+
+}  // namespace bfly

@@ -8,7 +8,8 @@ Logical (unsharded) tensors, all [out_features, in_features] row-major, bf16:
   global : embed[V,h]  pos_embed[P,h] (GPT-2)  final_norm.w[h] (.b GPT-2)  lm_head[V,h] (untied)
   layer  : attn_norm.w  wq[nh*d,h] wk[nkv*d,h] wv[nkv*d,h]  wo[h,nh*d]  ffn_norm.w
            dense : w_gate[f,h] (gated only)  w_up[f,h]  w_down[h,f]
-           MoE   : router[E,h]  e{i}.w_gate  e{i}.w_up  e{i}.w_down
+           MoE   : router[E,h]  e{i}.w_gate  e{i}.w_up  e{i}.w_down   (a rank's experts are stored
+                   concatenated: w_gate_up[E_l*2f,h] = [gate_e|up_e] blocks, w_down[h,E_l*f])
            GPT-2 : attn_norm.b bq bk bv bo ffn_norm.b b_up b_down
 
 `shard_spec` says how each rank tensor is assembled from rectangular blocks of the logical
@@ -199,6 +200,7 @@ class Piece:
     c0: int
     c1: int
     dst_row: int
+    dst_col: int = 0
 
 
 @dataclass(frozen=True)
@@ -251,10 +253,15 @@ def shard_spec(plan: PartitionPlan, rank: int) -> List[ShardTensor]:
             whole(p + "b_down", "b_down", l)
         if cfg.is_moe:
             whole(p + "router", "router", l)
-            for e in rp.experts:
-                out.append(ShardTensor(p + f"experts.{e}.w_gate_up", 2 * f, h, (
-                    Piece(f"e{e}.w_gate", l, 0, f, 0, h, 0), Piece(f"e{e}.w_up", l, 0, f, 0, h, f))))
-                out.append(ShardTensor(p + f"experts.{e}.w_down", h, f, (Piece(f"e{e}.w_down", l, 0, h, 0, f, 0),)))
+            # local experts are concatenated: w_gate_up rows = [gate_e | up_e] per expert block, w_down
+            # columns = expert blocks, so the expert FFNs run as ONE column- and ONE row-parallel GEMM
+            ne = len(rp.experts)
+            gu, dn = [], []
+            for j, e in enumerate(rp.experts):
+                gu += [Piece(f"e{e}.w_gate", l, 0, f, 0, h, j * 2 * f), Piece(f"e{e}.w_up", l, 0, f, 0, h, j * 2 * f + f)]
+                dn.append(Piece(f"e{e}.w_down", l, 0, h, 0, f, 0, j * f))
+            out.append(ShardTensor(p + "w_gate_up", ne * 2 * f, h, tuple(gu)))
+            out.append(ShardTensor(p + "w_down", h, ne * f, tuple(dn)))
         else:
             f0, f1 = rp.ffn_cols
             nf = f1 - f0
@@ -290,7 +297,8 @@ def shard_weights(source, plan: PartitionPlan, rank: int) -> RankWeights:
     for st in shard_spec(plan, rank):
         t = torch.empty((st.rows, st.cols), dtype=torch.bfloat16)
         for pc in st.pieces:
-            t[pc.dst_row:pc.dst_row + (pc.r1 - pc.r0)] = source.block(pc.name, pc.layer, pc.r0, pc.r1, pc.c0, pc.c1)
+            t[pc.dst_row:pc.dst_row + (pc.r1 - pc.r0), pc.dst_col:pc.dst_col + (pc.c1 - pc.c0)] = \
+                source.block(pc.name, pc.layer, pc.r0, pc.r1, pc.c0, pc.c1)
         tensors[st.name] = t.reshape(-1) if st.cols == 1 else t
     return RankWeights(plan, rank, tensors)
 

@@ -1,0 +1,141 @@
+/*
+ * butterfly_b200 -- C ABI of the B200-native partitioned transformer block forward.
+ *
+ * Drop-in boundary.  The reference repository TensorHusker/Butterfly defines
+ * no plugin / operator / FFI interface for this path: it contains no source at all
+ * (ref:CLAUDE.md:13-15 "newly initialized repository ... Expected Architecture (To Be
+ * Implemented)"; the intended engine / partitioning / communication components are one-line
+ * bullets at ref:CLAUDE.md:19-21).  Each entry point below therefore cites the intended component
+ * it realises instead of a reference function.
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every function returns 0 on success
+ * or a BFLY_E* code, and never throws; bfly_last_error() gives the message (per calling thread,
+ * and sticky on the ctx).  One process per GPU rank, one host thread per ctx, one CUDA stream per
+ * ctx; functions are not re-entrant on the same ctx.  The ctx owns all device memory (weights, KV
+ * pages, workspaces); host buffers and device pointers passed to bfly_k_* are borrowed for the call.
+ * There is no CPU fallback anywhere behind this header.
+ */
+#ifndef BUTTERFLY_B200_H
+#define BUTTERFLY_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BFLY_OK 0
+#define BFLY_EINVAL 1
+#define BFLY_ECUDA 2
+#define BFLY_ENCCL 3
+#define BFLY_ESTATE 4
+#define BFLY_ENOMEM 5
+
+#define BFLY_FAMILY_GPT2 0
+#define BFLY_FAMILY_LLAMA 1
+#define BFLY_FAMILY_MIXTRAL 2
+
+typedef struct bfly_ctx bfly_ctx;
+
+/* Model shape + this rank's place in the tensor-parallel plan (butterfly_b200/plan.py). */
+typedef struct bfly_model_desc {
+  int32_t family;
+  int32_t hidden, n_layers, n_heads, n_kv_heads, head_dim, ffn, vocab;
+  int32_t n_experts, top_k;
+  float norm_eps;
+  float rope_theta;            /* 0 => learned absolute positions */
+  int32_t max_pos;
+  int32_t tied_head, bias;
+  int32_t tp, rank;            /* tensor-parallel degree and this rank */
+  int32_t page_size;           /* tokens per KV page (power of two) */
+  int32_t max_batch;           /* sequences resident in the KV cache */
+  int32_t max_ctx;             /* KV capacity per sequence, tokens */
+  int32_t max_tokens;          /* rows of one forward chunk (prefill is chunked to this) */
+} bfly_model_desc;
+
+typedef struct bfly_stats {
+  uint64_t kernel_launches;    /* kernels of this library launched so far (graph replays included) */
+  uint64_t weight_bytes;       /* device bytes held by weights */
+  uint64_t kv_bytes;           /* device bytes held by the paged KV cache */
+  uint64_t workspace_bytes;    /* device bytes held by activations / split-K scratch */
+  int32_t sm_count;
+  int32_t graph_nodes_decode;  /* kernel nodes in the last captured decode step */
+} bfly_stats;
+
+int bfly_version(void);
+/* ctx may be NULL: returns the calling thread's last error. */
+const char* bfly_last_error(const bfly_ctx* ctx);
+
+/* ---- engine: intended "Distributed Inference Engine" (ref:CLAUDE.md:19) ------------------- */
+int bfly_create(const bfly_model_desc* desc, int device, bfly_ctx** out);
+int bfly_destroy(bfly_ctx* ctx);
+int bfly_get_stats(const bfly_ctx* ctx, bfly_stats* out);
+
+/* ---- weights: intended "Model Partitioning" (ref:CLAUDE.md:21); names = shard_spec() names -- */
+int bfly_upload_weight(bfly_ctx* ctx, const char* name, const void* host_bf16, int64_t rows, int64_t cols);
+int bfly_alloc_weight(bfly_ctx* ctx, const char* name, int64_t rows, int64_t cols);
+/* Fill rows [dst_row, +rows) x cols [dst_col, +cols) of an allocated weight with the synthetic
+ * block [r0.., c0..] of the logical tensor `key` (bit-identical to weights.synth_block). */
+int bfly_fill_weight_block(bfly_ctx* ctx, const char* name, int64_t dst_row, int64_t dst_col, uint64_t key,
+                           int64_t ncols_full, int64_t r0, int64_t c0, int64_t rows, int64_t cols, float scale,
+                           float offset);
+int bfly_read_weight(bfly_ctx* ctx, const char* name, void* host_bf16, int64_t max_bytes);
+int bfly_weights_ready(bfly_ctx* ctx);   /* validates names/shapes; required before any forward */
+
+/* ---- communication: intended "Communication Layer" (ref:CLAUDE.md:20), NCCL over NVLink ---- */
+int bfly_comm_unique_id(void* out_id128);                       /* rank 0; 128 bytes */
+int bfly_comm_init(bfly_ctx* ctx, const void* id128, int world, int rank);
+
+/* ---- forward ------------------------------------------------------------------------------- */
+/* Optional: install a page table int32[n_seqs][pages_per_seq] (default: sequence b owns pages
+ * b*pages_per_seq ...).  Physical page ids must be unique and < max_batch*pages_per_seq. */
+int bfly_set_page_table(bfly_ctx* ctx, const int32_t* table_host, int n_seqs, int pages_per_seq);
+/* Prefill: tokens_host int32[B][S]; restarts the KV cache of sequences 0..B-1.  logits_host
+ * (fp32 [B][vocab], last position, gathered over ranks) and next_tokens_host (int32[B]) may be NULL. */
+int bfly_prefill(bfly_ctx* ctx, const int32_t* tokens_host, int B, int S, float* logits_host,
+                 int32_t* next_tokens_host);
+/* One decode step: tokens_host int32[B] (NULL = continue from the engine's own greedy tokens). */
+int bfly_decode(bfly_ctx* ctx, const int32_t* tokens_host, int B, float* logits_host, int32_t* next_tokens_host);
+/* n free-running greedy steps with everything resident on the device (one CUDA graph replay per
+ * step, no host synchronisation until the end).  tokens_out_host int32[B][n_steps] = the token fed
+ * at each step; may be NULL. */
+int bfly_decode_greedy(bfly_ctx* ctx, int B, int n_steps, int32_t* tokens_out_host);
+/* Same, but only enqueues the steps on the ctx stream (for device-side timing); no copy, no sync. */
+int bfly_decode_enqueue(bfly_ctx* ctx, int B, int n_steps);
+int bfly_sync(bfly_ctx* ctx);
+void* bfly_stream(bfly_ctx* ctx);        /* the ctx's cudaStream_t, for event timing by the caller */
+
+/* ---- per-kernel entry points on raw device pointers (parity tests, profiling) -------------- */
+/* All run on `stream` (a cudaStream_t, may be NULL = legacy default stream) and do not allocate. */
+int bfly_k_fill_synth(void* dst_bf16, int64_t dst_pitch, uint64_t key, int64_t ncols_full, int64_t r0, int64_t c0,
+                      int64_t rows, int64_t cols, float scale, float offset, void* stream);
+int bfly_k_embed(const int32_t* tokens, const void* table_bf16, const void* pos_table_bf16, const int32_t* seq_lens,
+                 int S, float* residual, int T, int h, int vocab, void* stream);
+int bfly_k_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
+                    const void* bias_bf16, const void* gamma_bf16, const void* beta_bf16, float eps, int layer_norm,
+                    void* out_bf16, int T, int h, void* stream);
+int bfly_k_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, const void* bias_bf16,
+                   const float* rope_table, const int32_t* seq_lens, int S, int T, int nq, int nk, int head_dim,
+                   void* q_out_bf16, void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
+                   int page_size, void* stream);
+int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
+                       int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int T, int nq,
+                       float* part_o, float* part_ml, int n_splits, void* out_bf16, void* stream);
+int bfly_k_act(const float* in, int n_partials, int64_t partial_stride, const void* bias_bf16, int mode,
+               int n_blocks, int f_block, const float* route_w, void* out_bf16, int T, void* stream);
+int bfly_k_lm_finalize(const float* partials, int n_partials, int64_t partial_stride, int T, int v_local, int v0,
+                       float* logits, int64_t logits_ld, uint64_t* keys, int32_t* tokens_out, void* stream);
+int bfly_k_moe_router(const void* xn_bf16, const void* router_bf16, int T, int h, int n_experts, int top_k,
+                      int first_local, int n_local, float* route_w, void* stream);
+/* C[n][m] = sum_k W[m][k] X[n][k].  splits/bn/stages <= 0 pick the planner's choice; the chosen
+ * split count is returned through *splits_used.  out_f32 receives `splits` slices `split_stride`
+ * floats apart (row pitch ldc); out_bf16 (splits must resolve to 1) receives bf16 directly. */
+int bfly_k_gemm(const void* w_bf16, const void* x_bf16, int M, int N, int K, int64_t ldx, int splits, int bn,
+                int stages, float* out_f32, int64_t split_stride, void* out_bf16, int64_t ldc, int* splits_used,
+                void* stream);
+int bfly_k_gemm_plan(int M, int N, int K, int* splits, int* bn, int* stages);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BUTTERFLY_B200_H */

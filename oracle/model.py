@@ -80,14 +80,17 @@ class OracleModel:
                 for r in range(plan.tp):
                     w = self.w[r]
                     acc = torch.zeros_like(x)
-                    for e in plan.rank(r).experts:
+                    f = cfg.ffn
+                    for j, e in enumerate(plan.rank(r).experts):
                         sel = (idx == e)
                         rows = sel.any(-1).nonzero().squeeze(-1)
                         if rows.numel() == 0:
                             continue
-                        act = rq(ops.swiglu(ops.linear(hn[rows], w[p + f"experts.{e}.w_gate_up"])))
-                        y = ops.linear(act, w[p + f"experts.{e}.w_down"])
-                        acc[rows] += y * (gate_w[rows] * sel[rows]).sum(-1, keepdim=True)
+                        w_gu = w[p + "w_gate_up"][j * 2 * f:(j + 1) * 2 * f]
+                        w_dn = w[p + "w_down"][:, j * f:(j + 1) * f]
+                        gw = (gate_w[rows] * sel[rows]).sum(-1, keepdim=True)
+                        act = rq(ops.swiglu(ops.linear(hn[rows], w_gu)) * gw)
+                        acc[rows] += ops.linear(act, w_dn)
                     parts.append(acc)
             else:
                 for r in range(plan.tp):

@@ -1,0 +1,267 @@
+"""Per-kernel parity on a B200: every CUDA kernel, called through the C ABI on raw device pointers,
+against the oracle's corresponding function (oracle/ops.py) on the same seeded inputs.
+
+Tolerances: fp32 outputs (residual, split-K slices, logits, routing weights): max abs err 1e-4 x the
+value scale; bf16 outputs: within 1 bf16 ulp (2^-8 relative) of the rounded oracle value; integer
+outputs (tokens, synthetic weight bits): bit-exact.
+"""
+import ctypes as C
+import math
+
+import pytest
+import torch
+
+from butterfly_b200 import _lib
+from butterfly_b200.weights import synth_block, synth_scale, tensor_key
+from oracle import ops
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib(cuda):
+    return _lib.load()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ok(lib, rc):
+    _lib.check(rc)
+    torch.cuda.synchronize()
+
+
+def bf16_close(got: torch.Tensor, want_f32: torch.Tensor, extra_abs: float = 0.0):
+    want = want_f32.to(torch.bfloat16).float()
+    tol = want.abs() * 2.0 ** -7 + 1e-6 + extra_abs
+    bad = ((got.float().cpu() - want).abs() > tol)
+    assert not bad.any(), f"{int(bad.sum())} of {bad.numel()} elements off by more than 1 bf16 ulp; max abs err " \
+                          f"{(got.float().cpu() - want).abs().max().item():.3e}"
+
+
+def gen(shape, seed, scale=1.0, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype)
+
+
+# ---------------------------------------------------------------------------------------------
+def test_fill_synth_bit_exact(lib, cuda):
+    key = tensor_key(0, 3, "wq")
+    for (r0, r1, c0, c1, ncols, std, off) in [(0, 64, 0, 128, 128, 0.02, 0.0), (5, 77, 3, 250, 4096, 0.02, 0.0),
+                                              (0, 512, 0, 1, 1, 0.02, 1.0), (100, 101, 7, 4000, 4096, 0.002, 0.0)]:
+        want = synth_block(key, ncols, r0, r1, c0, c1, synth_scale(std), off)
+        got = torch.zeros((r1 - r0, c1 - c0), dtype=torch.bfloat16, device=cuda)
+        ok(lib, lib.bfly_k_fill_synth(got.data_ptr(), c1 - c0, key, ncols, r0, c0, r1 - r0, c1 - c0,
+                                      float(synth_scale(std)), off, stream()))
+        assert torch.equal(got.cpu().view(torch.int16), want.view(torch.int16))
+
+
+def test_embed(lib, cuda):
+    V, h, B, S = 300, 256, 3, 5
+    table, pos = gen((V, h), 1, 0.02, torch.bfloat16), gen((64, h), 2, 0.01, torch.bfloat16)
+    g = torch.Generator().manual_seed(3)
+    toks = torch.randint(0, V, (B * S,), generator=g, dtype=torch.int32)
+    lens = torch.tensor([0, 7, 11], dtype=torch.int32)
+    positions = (lens[:, None] + torch.arange(S)[None, :]).reshape(-1)
+    for use_pos in (False, True):
+        out = torch.empty((B * S, h), dtype=torch.float32, device=cuda)
+        ok(lib, lib.bfly_k_embed(toks.to(cuda).data_ptr(), table.to(cuda).data_ptr(),
+                                 pos.to(cuda).data_ptr() if use_pos else None, lens.to(cuda).data_ptr(), S,
+                                 out.data_ptr(), B * S, h, V, stream()))
+        want = ops.embed(toks, table.float(), pos.float() if use_pos else None, positions)
+        assert (out.cpu() - want).abs().max().item() < 1e-7
+
+
+@pytest.mark.parametrize("h,layer_norm,n_part", [(256, False, 0), (4096, False, 3), (768, True, 2), (8192, False, 1)])
+def test_add_norm(lib, cuda, h, layer_norm, n_part):
+    T = 7
+    res, parts = gen((T, h), 1), gen((max(n_part, 1), T, h), 2, 0.3)
+    bias, gamma, beta = gen((h,), 3, 0.1, torch.bfloat16), (1 + gen((h,), 4, 0.05)).to(torch.bfloat16), \
+        gen((h,), 5, 0.05, torch.bfloat16)
+    d_res, d_out = res.to(cuda), torch.empty((T, h), dtype=torch.bfloat16, device=cuda)
+    ok(lib, lib.bfly_k_add_norm(d_res.data_ptr(), parts.to(cuda).data_ptr() if n_part else None, n_part, T * h,
+                                bias.to(cuda).data_ptr(), gamma.to(cuda).data_ptr(),
+                                beta.to(cuda).data_ptr() if layer_norm else None, 1e-5, int(layer_norm),
+                                d_out.data_ptr(), T, h, stream()))
+    x = res.clone()
+    for p in range(n_part):
+        x = x + parts[p]
+    x = x + bias.float()
+    assert (d_res.cpu() - x).abs().max().item() < 1e-5
+    want = ops.norm(x, gamma.float(), beta.float() if layer_norm else None, 1e-5, layer_norm)
+    bf16_close(d_out, want, extra_abs=2e-5)
+
+
+GEMM_SHAPES = [
+    # M (weight rows), N (tokens), K
+    (128, 16, 64), (256, 32, 256), (384, 32, 4096), (1000, 7, 768), (6144, 32, 4096), (4096, 32, 1792),
+    (500, 100, 520), (256, 300, 1024), (3072, 64, 768), (128, 1, 8192), (2048, 512, 512),
+]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_split_slices(lib, cuda, M, N, K):
+    W, X = gen((M, K), 1, 0.05, torch.bfloat16).to(cuda), gen((N, K), 2, 1.0, torch.bfloat16).to(cuda)
+    want = (X.float() @ W.float().t()).cpu()                       # [N, M] fp32 reference on the same bf16 inputs
+    for splits in (0, 1, 3):
+        if splits > (K + 63) // 64:
+            continue
+        used = C.c_int32(0)
+        cap = 16
+        out = torch.full((cap, N, M), float("nan"), dtype=torch.float32, device=cuda)
+        ok(lib, lib.bfly_k_gemm(W.data_ptr(), X.data_ptr(), M, N, K, K, splits, 0, 0, out.data_ptr(), N * M, None, M,
+                                C.byref(used), stream()))
+        got = out[:used.value].sum(0).cpu()
+        assert not torch.isnan(got).any(), f"unwritten outputs with splits={used.value}"
+        err = (got - want).abs().max().item()
+        assert err < 2e-3 * max(1.0, want.abs().max().item()), f"splits={used.value} max err {err}"
+
+
+def test_gemm_bf16_out_and_pitched_x(lib, cuda):
+    M, N, K, S = 512, 6, 1024, 5
+    W = gen((M, K), 1, 0.05, torch.bfloat16).to(cuda)
+    Xall = gen((N * S, K), 2, 1.0, torch.bfloat16).to(cuda)
+    X_last = Xall.view(N, S, K)[:, S - 1]                           # rows b*S + S-1, pitch S*K
+    want = (X_last.float() @ W.float().t()).cpu()
+    out = torch.zeros((N, M), dtype=torch.bfloat16, device=cuda)
+    used = C.c_int32(0)
+    ok(lib, lib.bfly_k_gemm(W.data_ptr(), Xall.data_ptr() + (S - 1) * K * 2, M, N, K, S * K, 1, 0, 0, None, 0,
+                            out.data_ptr(), M, C.byref(used), stream()))
+    assert used.value == 1
+    bf16_close(out, want, extra_abs=2e-3)
+
+
+@pytest.mark.parametrize("d,nq,nk,theta,use_bias", [(128, 4, 1, 5e5, False), (64, 6, 6, 0.0, True), (32, 4, 2, 1e6, False)])
+def test_rope_kv(lib, cuda, d, nq, nk, theta, use_bias):
+    B, S, ps, pps, n_part = 3, 4, 16, 4, 2
+    T, ld = B * S, (nq + 2 * nk) * d
+    lens = torch.tensor([0, 9, 21], dtype=torch.int32)
+    qkv = gen((n_part, T, ld), 1, 0.7)
+    bias = gen((ld,), 2, 0.1, torch.bfloat16)
+    perm = torch.randperm(B * pps, generator=torch.Generator().manual_seed(5)).to(torch.int32).reshape(B, pps)
+    pages = torch.zeros((B * pps, 2, nk, ps, d), dtype=torch.bfloat16, device=cuda)
+    half = d // 2
+    max_pos = 64
+    inv = theta ** (-torch.arange(0, half, dtype=torch.float64) * 2.0 / d) if theta > 0 else None
+    table = None
+    if theta > 0:
+        ang = torch.arange(max_pos, dtype=torch.float64)[:, None] * inv[None, :]
+        table = torch.stack([ang.cos().float(), ang.sin().float()], dim=-1).contiguous().to(cuda)   # [pos, half, 2]
+    q_out = torch.zeros((T, nq * d), dtype=torch.bfloat16, device=cuda)
+    ok(lib, lib.bfly_k_rope_kv(qkv.to(cuda).data_ptr(), n_part, T * ld, bias.to(cuda).data_ptr() if use_bias else None,
+                               table.data_ptr() if table is not None else None, lens.to(cuda).data_ptr(), S, T, nq, nk,
+                               d, q_out.data_ptr(), pages.data_ptr(), perm.to(cuda).data_ptr(), pps, ps, stream()))
+    x = qkv.sum(0) + (bias.float() if use_bias else 0.0)
+    positions = (lens[:, None] + torch.arange(S)[None, :]).reshape(-1)
+    q = x[:, :nq * d].reshape(T, nq, d)
+    k = x[:, nq * d:(nq + nk) * d].reshape(T, nk, d)
+    v = x[:, (nq + nk) * d:].reshape(T, nk, d)
+    if theta > 0:
+        q, k = ops.rope(q, positions, theta), ops.rope(k, positions, theta)
+    bf16_close(q_out, q.reshape(T, nq * d), extra_abs=1e-5)
+    pg = pages.cpu()
+    for t in range(T):
+        b, pos = t // S, int(positions[t])
+        page, slot = int(perm[b, pos // ps]), pos % ps
+        bf16_close(pg[page, 0, :, slot, :], k[t], extra_abs=1e-5)
+        bf16_close(pg[page, 1, :, slot, :], v[t], extra_abs=1e-5)
+
+
+@pytest.mark.parametrize("d,nq,nk,ctx_lens,n_splits", [
+    (128, 4, 1, [1, 33, 257], 1), (128, 8, 2, [100, 5, 64], 4), (128, 8, 1, [300, 17, 96], 3),
+    (64, 6, 6, [40, 41, 2], 2), (32, 8, 4, [70, 1, 128], 5), (128, 4, 1, [2048, 1999, 31], 9)])
+def test_attn_decode(lib, cuda, d, nq, nk, ctx_lens, n_splits):
+    B, ps = len(ctx_lens), 32
+    pps = (max(ctx_lens) + ps - 1) // ps
+    g = torch.Generator().manual_seed(7)
+    perm = torch.randperm(B * pps, generator=g).to(torch.int32).reshape(B, pps)
+    pages = gen((B * pps, 2, nk, ps, d), 8, 1.0, torch.bfloat16)
+    q = gen((B, nq * d), 9, 1.0, torch.bfloat16)
+    lens = torch.tensor([c - 1 for c in ctx_lens], dtype=torch.int32)        # tokens cached before the query
+    out = torch.zeros((B, nq * d), dtype=torch.bfloat16, device=cuda)
+    part_o = torch.zeros((B * nq * n_splits * d,), dtype=torch.float32, device=cuda)
+    part_ml = torch.zeros((B * nq * n_splits * 2,), dtype=torch.float32, device=cuda)
+    ok(lib, lib.bfly_k_attn_decode(q.to(cuda).data_ptr(), pages.to(cuda).data_ptr(), perm.to(cuda).data_ptr(), pps, ps,
+                                   nk, d, lens.to(cuda).data_ptr(), 1, B, nq, part_o.data_ptr(), part_ml.data_ptr(),
+                                   n_splits, out.data_ptr(), stream()))
+    for b, ctx in enumerate(ctx_lens):
+        pos = torch.arange(ctx)
+        kv = pages[perm[b, pos // ps].long(), :, :, pos % ps, :].float()      # [ctx, 2, nk, d]
+        want = ops.attention(q[b].float().reshape(1, 1, nq, d), kv[:, 0][None], kv[:, 1][None], ctx - 1)
+        bf16_close(out[b], want.reshape(-1), extra_abs=2e-5)
+
+
+def test_attn_prefill_rows(lib, cuda):
+    """S new tokens per sequence: token s of sequence b sees lens[b] + s + 1 keys (causal)."""
+    d, nq, nk, ps, S = 64, 4, 2, 16, 5
+    lens0 = [0, 11]
+    B = len(lens0)
+    pps = 2
+    pages = gen((B * pps, 2, nk, ps, d), 8, 1.0, torch.bfloat16)
+    table = torch.arange(B * pps, dtype=torch.int32).reshape(B, pps)
+    q = gen((B * S, nq * d), 9, 1.0, torch.bfloat16)
+    out = torch.zeros((B * S, nq * d), dtype=torch.bfloat16, device=cuda)
+    n_splits = 2
+    part_o = torch.zeros((B * S * nq * n_splits * d,), dtype=torch.float32, device=cuda)
+    part_ml = torch.zeros((B * S * nq * n_splits * 2,), dtype=torch.float32, device=cuda)
+    ok(lib, lib.bfly_k_attn_decode(q.to(cuda).data_ptr(), pages.to(cuda).data_ptr(), table.to(cuda).data_ptr(), pps, ps,
+                                   nk, d, torch.tensor(lens0, dtype=torch.int32).to(cuda).data_ptr(), S, B * S, nq,
+                                   part_o.data_ptr(), part_ml.data_ptr(), n_splits, out.data_ptr(), stream()))
+    for b in range(B):
+        ctx = lens0[b] + S
+        pos = torch.arange(ctx)
+        kv = pages[table[b, pos // ps].long(), :, :, pos % ps, :].float()
+        want = ops.attention(q[b * S:(b + 1) * S].float().reshape(1, S, nq, d), kv[:, 0][None], kv[:, 1][None], lens0[b])
+        bf16_close(out[b * S:(b + 1) * S], want.reshape(S, nq * d), extra_abs=2e-5)
+
+
+@pytest.mark.parametrize("mode,n_blocks,fb,n_part,routed", [(0, 1, 512, 2, False), (1, 1, 3072, 1, False), (0, 4, 256, 3, True)])
+def test_act(lib, cuda, mode, n_blocks, fb, n_part, routed):
+    T = 5
+    f_out = n_blocks * fb
+    ld = f_out * (2 if mode == 0 else 1)
+    x = gen((n_part, T, ld), 1, 1.5)
+    bias = gen((f_out,), 2, 0.1, torch.bfloat16)
+    rw = torch.rand((T, n_blocks), generator=torch.Generator().manual_seed(3))
+    rw[rw < 0.4] = 0.0
+    out = torch.zeros((T, f_out), dtype=torch.bfloat16, device=cuda)
+    ok(lib, lib.bfly_k_act(x.to(cuda).data_ptr(), n_part, T * ld, bias.to(cuda).data_ptr() if mode == 1 else None, mode,
+                           n_blocks, fb, rw.to(cuda).data_ptr() if routed else None, out.data_ptr(), T, stream()))
+    s = x.sum(0)
+    if mode == 0:
+        want = ops.swiglu(s.reshape(T, n_blocks, 2 * fb)).reshape(T, f_out)
+    else:
+        want = ops.gelu_tanh(s + bias.float())
+    if routed:
+        want = (want.reshape(T, n_blocks, fb) * rw[:, :, None]).reshape(T, f_out)
+    bf16_close(out, want, extra_abs=1e-5)
+
+
+def test_lm_finalize_and_argmax(lib, cuda):
+    T, V, n_part, v0 = 6, 5003, 3, 1000
+    parts = gen((n_part, T, V), 1, 0.3)
+    parts[:, 2, 77] = 1.0
+    parts[:, 2, 4000] = 1.0            # exact tie: lowest index must win
+    logits = torch.zeros((T, V + 5), dtype=torch.float32, device=cuda)
+    keys = torch.zeros((T,), dtype=torch.int64, device=cuda)
+    toks = torch.zeros((T,), dtype=torch.int32, device=cuda)
+    ok(lib, lib.bfly_k_lm_finalize(parts.to(cuda).data_ptr(), n_part, T * V, T, V, v0, logits.data_ptr(), V + 5,
+                                   keys.data_ptr(), toks.data_ptr(), stream()))
+    want = parts[0] + parts[1] + parts[2]
+    assert (logits[:, :V].cpu() - want).abs().max().item() < 1e-6
+    assert torch.equal(toks.cpu(), ops.argmax(logits[:, :V].cpu()) + v0)
+    assert int(toks[2]) == v0 + 77
+
+
+def test_moe_router(lib, cuda):
+    T, h, E, k = 9, 512, 8, 2
+    xn, wr = gen((T, h), 1, 1.0, torch.bfloat16), gen((E, h), 2, 0.05, torch.bfloat16)
+    idx, w = ops.moe_router(xn.float(), wr.float(), k)
+    for first, n_local in ((0, 8), (4, 4), (6, 2)):
+        out = torch.zeros((T, n_local), dtype=torch.float32, device=cuda)
+        ok(lib, lib.bfly_k_moe_router(xn.to(cuda).data_ptr(), wr.to(cuda).data_ptr(), T, h, E, k, first, n_local,
+                                      out.data_ptr(), stream()))
+        want = torch.zeros((T, E))
+        want.scatter_(1, idx, w)
+        assert (out.cpu() - want[:, first:first + n_local]).abs().max().item() < 1e-5

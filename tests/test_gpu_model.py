@@ -1,0 +1,125 @@
+"""End-to-end parity on a B200: Model (C ABI, CUDA) vs OracleModel (CPU fp32) on identical seeded
+weights and tokens.  Gate (BASELINE.json north_star): max abs err <= 1e-2 on logits at every
+teacher-forced step; greedy tokens identical wherever the oracle's own top-1/top-2 margin exceeds
+twice that tolerance (a flat random-init vocabulary makes closer calls a coin flip for ANY bf16
+pipeline -- BASELINE.md "Parity protocol"); every disagreement is reported with its margin.
+"""
+import pytest
+import torch
+
+from butterfly_b200 import (LLAMA3_8B, SyntheticSource, make_plan, shard_weights, synthetic_tokens, tiny)
+from oracle import OracleModel, ops
+
+pytestmark = pytest.mark.gpu
+
+LOGIT_TOL = 1e-2
+
+
+def _margins(logits: torch.Tensor) -> torch.Tensor:
+    top2 = logits.topk(2, dim=-1).values
+    return top2[:, 0] - top2[:, 1]
+
+
+def _run_parity(cfg, B, S, n_steps, device_synth, max_ctx=None, page_table=None):
+    from butterfly_b200 import Model
+    src = SyntheticSource(cfg, 0)
+    plan = make_plan(cfg, 1)
+    rw = shard_weights(src, plan, 0)
+    om = OracleModel(plan, [rw])
+    gm = Model(plan, 0, src if device_synth else rw, max_batch=B, max_ctx=max_ctx or (S + n_steps + 1))
+    if page_table is not None:
+        gm.set_page_table(page_table)
+    toks = synthetic_tokens(cfg, B, S)
+    lo, lg = om.prefill(toks), gm.prefill(toks)
+    worst, flips, close_calls = (lo - lg).abs().max().item(), [], 0
+    for step in range(n_steps):
+        want_tok, got_tok = ops.argmax(lo), ops.argmax(lg)
+        margin = _margins(lo)
+        for b in range(B):
+            if int(want_tok[b]) != int(got_tok[b]):
+                flips.append((step, b, float(margin[b])))
+            close_calls += int(margin[b] <= 2 * LOGIT_TOL)
+        assert torch.equal(gm.last_tokens, got_tok), "engine greedy token != argmax of its own logits"
+        lo, lg = om.decode(want_tok), gm.decode(want_tok)          # teacher-forced with the oracle's token
+        worst = max(worst, (lo - lg).abs().max().item())
+    gm.close()
+    print(f"\n[{cfg.name}] B={B} S={S} steps={n_steps}: max|dlogit|={worst:.3e} logit_std={lo.std().item():.3f} "
+          f"close_calls={close_calls} flips={flips}")
+    assert worst <= LOGIT_TOL, f"logits differ from the oracle by {worst}"
+    bad = [f for f in flips if f[2] > 2 * LOGIT_TOL]
+    assert not bad, f"greedy token mismatch at positions with a clear oracle margin: {bad}"
+    return worst
+
+
+@pytest.mark.parametrize("family", ["llama", "gpt2", "mixtral"])
+def test_tiny_parity(cuda, family):
+    _run_parity(tiny(family), B=3, S=11, n_steps=6, device_synth=False)
+
+
+def test_tiny_parity_device_synth_and_shuffled_pages(cuda):
+    cfg = tiny("llama")
+    B, S, steps = 4, 40, 8
+    max_ctx = 64
+    pps = (max_ctx + 31) // 32
+    perm = torch.randperm(B * pps, generator=torch.Generator().manual_seed(11)).to(torch.int32).reshape(B, pps)
+    _run_parity(cfg, B=B, S=S, n_steps=steps, device_synth=True, max_ctx=max_ctx, page_table=perm)
+
+
+def test_device_synth_weights_bit_exact(cuda):
+    from butterfly_b200 import Model
+    cfg = tiny("mixtral")
+    plan = make_plan(cfg, 2)
+    src = SyntheticSource(cfg, 0)
+    for rank in (0, 1):
+        rw = shard_weights(src, plan, rank)
+        gm = Model(plan, rank, src, max_batch=2, max_ctx=32)
+        for name, t in rw.tensors.items():
+            t2 = t if t.dim() == 2 else t.reshape(-1, 1)
+            got = gm.read_weight(name, t2.shape[0], t2.shape[1])
+            assert torch.equal(got.view(torch.int16), t2.view(torch.int16)), name
+        gm.close()
+
+
+def test_free_running_greedy_matches_teacher_forced(cuda):
+    """decode_greedy (CUDA-graph replays, device-resident tokens) == step-by-step decode()."""
+    from butterfly_b200 import Model
+    cfg = tiny("llama")
+    plan = make_plan(cfg, 1)
+    src = SyntheticSource(cfg, 0)
+    toks = synthetic_tokens(cfg, 4, 9)
+    gm = Model(plan, 0, src, max_batch=4, max_ctx=64)
+    gm.prefill(toks)
+    fed = gm.decode_greedy(12)
+    gm.prefill(toks)
+    ref = []
+    for _ in range(12):
+        ref.append(gm.last_tokens.clone())
+        gm.decode(None)
+    gm.close()
+    assert torch.equal(fed, torch.stack(ref, dim=1))
+    om = OracleModel(plan, [shard_weights(src, plan, 0)])
+    om.prefill(toks)
+    want = om.decode_greedy(12)
+    agree = (want == fed).float().mean().item()
+    print(f"\nfree-running greedy agreement with the oracle over 4x12 tokens: {agree:.3f}")
+
+
+def test_llama3_8b_width_shallow_parity(cuda):
+    """Full Llama-3-8B width (h=4096, 32/8 heads, f=14336, V=128256), depth 2, B=4, prefill 48 + 4 steps."""
+    _run_parity(LLAMA3_8B.with_layers(2), B=4, S=48, n_steps=4, device_synth=True)
+
+
+def test_errors_are_reported(cuda):
+    from butterfly_b200 import Model
+    from butterfly_b200._lib import BflyError
+    cfg = tiny("llama")
+    plan = make_plan(cfg, 1)
+    gm = Model(plan, 0, SyntheticSource(cfg, 0), max_batch=2, max_ctx=16)
+    with pytest.raises(BflyError):
+        gm.prefill(synthetic_tokens(cfg, 3, 4))          # batch > max_batch
+    with pytest.raises(BflyError):
+        gm.prefill(synthetic_tokens(cfg, 2, 17))         # prompt > max_ctx
+    gm.prefill(synthetic_tokens(cfg, 2, 16))
+    with pytest.raises(BflyError):
+        gm.decode(None)                                  # KV cache full
+    gm.close()
