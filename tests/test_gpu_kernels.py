@@ -40,6 +40,24 @@ def bf16_close(got: torch.Tensor, want_f32: torch.Tensor, extra_abs: float = 0.0
                           f"{(got.float().cpu() - want).abs().max().item():.3e}"
 
 
+_keep = []
+
+
+def D(t: torch.Tensor) -> int:
+    """Device pointer of a CUDA copy of `t` that stays alive for the whole test (a temporary would be
+    freed -- and its block reused by the next copy -- before the kernel is even launched)."""
+    d = t.to("cuda").contiguous()
+    _keep.append(d)
+    return d.data_ptr()
+
+
+@pytest.fixture(autouse=True)
+def _release_keepalive():
+    yield
+    torch.cuda.synchronize()
+    _keep.clear()
+
+
 def gen(shape, seed, scale=1.0, dtype=torch.float32):
     g = torch.Generator().manual_seed(seed)
     return (torch.randn(shape, generator=g) * scale).to(dtype)
@@ -66,8 +84,8 @@ def test_embed(lib, cuda):
     positions = (lens[:, None] + torch.arange(S)[None, :]).reshape(-1)
     for use_pos in (False, True):
         out = torch.empty((B * S, h), dtype=torch.float32, device=cuda)
-        ok(lib, lib.bfly_k_embed(toks.to(cuda).data_ptr(), table.to(cuda).data_ptr(),
-                                 pos.to(cuda).data_ptr() if use_pos else None, lens.to(cuda).data_ptr(), S,
+        ok(lib, lib.bfly_k_embed(D(toks), D(table),
+                                 D(pos) if use_pos else None, D(lens), S,
                                  out.data_ptr(), B * S, h, V, stream()))
         want = ops.embed(toks, table.float(), pos.float() if use_pos else None, positions)
         assert (out.cpu() - want).abs().max().item() < 1e-7
@@ -80,9 +98,9 @@ def test_add_norm(lib, cuda, h, layer_norm, n_part):
     bias, gamma, beta = gen((h,), 3, 0.1, torch.bfloat16), (1 + gen((h,), 4, 0.05)).to(torch.bfloat16), \
         gen((h,), 5, 0.05, torch.bfloat16)
     d_res, d_out = res.to(cuda), torch.empty((T, h), dtype=torch.bfloat16, device=cuda)
-    ok(lib, lib.bfly_k_add_norm(d_res.data_ptr(), parts.to(cuda).data_ptr() if n_part else None, n_part, T * h,
-                                bias.to(cuda).data_ptr(), gamma.to(cuda).data_ptr(),
-                                beta.to(cuda).data_ptr() if layer_norm else None, 1e-5, int(layer_norm),
+    ok(lib, lib.bfly_k_add_norm(d_res.data_ptr(), D(parts) if n_part else None, n_part, T * h,
+                                D(bias), D(gamma),
+                                D(beta) if layer_norm else None, 1e-5, int(layer_norm),
                                 d_out.data_ptr(), T, h, stream()))
     x = res.clone()
     for p in range(n_part):
@@ -149,9 +167,9 @@ def test_rope_kv(lib, cuda, d, nq, nk, theta, use_bias):
         ang = torch.arange(max_pos, dtype=torch.float64)[:, None] * inv[None, :]
         table = torch.stack([ang.cos().float(), ang.sin().float()], dim=-1).contiguous().to(cuda)   # [pos, half, 2]
     q_out = torch.zeros((T, nq * d), dtype=torch.bfloat16, device=cuda)
-    ok(lib, lib.bfly_k_rope_kv(qkv.to(cuda).data_ptr(), n_part, T * ld, bias.to(cuda).data_ptr() if use_bias else None,
-                               table.data_ptr() if table is not None else None, lens.to(cuda).data_ptr(), S, T, nq, nk,
-                               d, q_out.data_ptr(), pages.data_ptr(), perm.to(cuda).data_ptr(), pps, ps, stream()))
+    ok(lib, lib.bfly_k_rope_kv(D(qkv), n_part, T * ld, D(bias) if use_bias else None,
+                               table.data_ptr() if table is not None else None, D(lens), S, T, nq, nk,
+                               d, q_out.data_ptr(), pages.data_ptr(), D(perm), pps, ps, stream()))
     x = qkv.sum(0) + (bias.float() if use_bias else 0.0)
     positions = (lens[:, None] + torch.arange(S)[None, :]).reshape(-1)
     q = x[:, :nq * d].reshape(T, nq, d)
@@ -182,8 +200,8 @@ def test_attn_decode(lib, cuda, d, nq, nk, ctx_lens, n_splits):
     out = torch.zeros((B, nq * d), dtype=torch.bfloat16, device=cuda)
     part_o = torch.zeros((B * nq * n_splits * d,), dtype=torch.float32, device=cuda)
     part_ml = torch.zeros((B * nq * n_splits * 2,), dtype=torch.float32, device=cuda)
-    ok(lib, lib.bfly_k_attn_decode(q.to(cuda).data_ptr(), pages.to(cuda).data_ptr(), perm.to(cuda).data_ptr(), pps, ps,
-                                   nk, d, lens.to(cuda).data_ptr(), 1, B, nq, part_o.data_ptr(), part_ml.data_ptr(),
+    ok(lib, lib.bfly_k_attn_decode(D(q), D(pages), D(perm), pps, ps,
+                                   nk, d, D(lens), 1, B, nq, part_o.data_ptr(), part_ml.data_ptr(),
                                    n_splits, out.data_ptr(), stream()))
     for b, ctx in enumerate(ctx_lens):
         pos = torch.arange(ctx)
@@ -205,8 +223,8 @@ def test_attn_prefill_rows(lib, cuda):
     n_splits = 2
     part_o = torch.zeros((B * S * nq * n_splits * d,), dtype=torch.float32, device=cuda)
     part_ml = torch.zeros((B * S * nq * n_splits * 2,), dtype=torch.float32, device=cuda)
-    ok(lib, lib.bfly_k_attn_decode(q.to(cuda).data_ptr(), pages.to(cuda).data_ptr(), table.to(cuda).data_ptr(), pps, ps,
-                                   nk, d, torch.tensor(lens0, dtype=torch.int32).to(cuda).data_ptr(), S, B * S, nq,
+    ok(lib, lib.bfly_k_attn_decode(D(q), D(pages), D(table), pps, ps,
+                                   nk, d, D(torch.tensor(lens0, dtype=torch.int32)), S, B * S, nq,
                                    part_o.data_ptr(), part_ml.data_ptr(), n_splits, out.data_ptr(), stream()))
     for b in range(B):
         ctx = lens0[b] + S
@@ -226,8 +244,8 @@ def test_act(lib, cuda, mode, n_blocks, fb, n_part, routed):
     rw = torch.rand((T, n_blocks), generator=torch.Generator().manual_seed(3))
     rw[rw < 0.4] = 0.0
     out = torch.zeros((T, f_out), dtype=torch.bfloat16, device=cuda)
-    ok(lib, lib.bfly_k_act(x.to(cuda).data_ptr(), n_part, T * ld, bias.to(cuda).data_ptr() if mode == 1 else None, mode,
-                           n_blocks, fb, rw.to(cuda).data_ptr() if routed else None, out.data_ptr(), T, stream()))
+    ok(lib, lib.bfly_k_act(D(x), n_part, T * ld, D(bias) if mode == 1 else None, mode,
+                           n_blocks, fb, D(rw) if routed else None, out.data_ptr(), T, stream()))
     s = x.sum(0)
     if mode == 0:
         want = ops.swiglu(s.reshape(T, n_blocks, 2 * fb)).reshape(T, f_out)
@@ -246,7 +264,7 @@ def test_lm_finalize_and_argmax(lib, cuda):
     logits = torch.zeros((T, V + 5), dtype=torch.float32, device=cuda)
     keys = torch.zeros((T,), dtype=torch.int64, device=cuda)
     toks = torch.zeros((T,), dtype=torch.int32, device=cuda)
-    ok(lib, lib.bfly_k_lm_finalize(parts.to(cuda).data_ptr(), n_part, T * V, T, V, v0, logits.data_ptr(), V + 5,
+    ok(lib, lib.bfly_k_lm_finalize(D(parts), n_part, T * V, T, V, v0, logits.data_ptr(), V + 5,
                                    keys.data_ptr(), toks.data_ptr(), stream()))
     want = parts[0] + parts[1] + parts[2]
     assert (logits[:, :V].cpu() - want).abs().max().item() < 1e-6
@@ -260,7 +278,7 @@ def test_moe_router(lib, cuda):
     idx, w = ops.moe_router(xn.float(), wr.float(), k)
     for first, n_local in ((0, 8), (4, 4), (6, 2)):
         out = torch.zeros((T, n_local), dtype=torch.float32, device=cuda)
-        ok(lib, lib.bfly_k_moe_router(xn.to(cuda).data_ptr(), wr.to(cuda).data_ptr(), T, h, E, k, first, n_local,
+        ok(lib, lib.bfly_k_moe_router(D(xn), D(wr), T, h, E, k, first, n_local,
                                       out.data_ptr(), stream()))
         want = torch.zeros((T, E))
         want.scatter_(1, idx, w)
