@@ -1,182 +1,263 @@
 // K6: paged-KV attention for one query token per (virtual) sequence, GQA-aware, split over the
-// context.  HBM-bound: K and V rows are streamed exactly once with
-// coalesced row-contiguous loads (a warp reads one 2*D-byte row per instruction, TB rows in flight),
-// all math in fp32 with an online softmax in the exp2 domain.
+// context.  HBM-bound: every K / V byte is read exactly once.
 //
-// Work split: grid (split, kv head, token).  A CTA's 4 warps interleave over batches of TB = 32/G
-// cached tokens; the TB*G = 32 partial dot products a lane accumulates are folded with a 31-shuffle
-// transpose-reduction so lane L ends up owning the score of (token L/G, head L%G).  Warps are merged
-// through shared memory, splits through a small fp32 scratch (part_o / part_ml) and a combine kernel.
-// Also used for prefill (token t of sequence b sees seq_lens[b] + s + 1 keys) until a tiled
-// tensor-core prefill kernel replaces it.
+// Data movement: a 32-token tile of one KV head is two contiguous 32*D*2-byte blocks in the paged
+// cache (K rows, and V stored TRANSPOSED [D][32]); each warp streams its tiles with two bulk async
+// copies (cp.async.bulk -> UBLKCP, mbarrier complete_tx) into a private 3-stage shared-memory ring,
+// so 4 warps keep up to 192 KB in flight per SM with no registers tied up.
+//
+// Math: tensor cores through mma.sync m16n8k16 (bf16 in, fp32 accumulate) in the transposed
+// formulation  S^T[token, head] = K[token, :] . Q[head, :]^T  and  O^T[d, head] = V^T[d, token] . P^T,
+// i.e. the cache tiles are always the row-major A operand and the <= 8 query heads of the GQA group
+// are the N = 8 columns, so no accumulator rows are padding.  The contraction indices (d for QK,
+// token for PV) are permuted so every thread reads 16 contiguous bytes per fragment; K rows carry
+// a 16-byte-chunk XOR swizzle (chunk ^ 4*(token&1)), applied when the cache is written, that makes
+// those reads bank-conflict free.  P goes from the S^T accumulator layout to the B-operand layout
+// with movmatrix.  Online softmax in the exp2 domain, fp32.
+//
+// Work split: grid (split, kv head, token); the 4 warps of a CTA interleave over the CTA's tiles,
+// are merged through shared memory, and splits are merged by attn_combine_kernel through the fp32
+// scratch part_o / part_ml.
 #include "kernels.cuh"
 
 namespace bfly {
 
 namespace {
 
-template <int N>
-struct TransposeReduce {
-  // v[0..N) per lane -> after log2(N) exchange steps v[0] of lane L holds sum over lanes of v[L's index]
-  static __device__ __forceinline__ void run(float* v, int lane) {
-    constexpr int H = N / 2;
-    const bool upper = (lane & H) != 0;
-#pragma unroll
-    for (int i = 0; i < H; ++i) {
-      const float send = upper ? v[i] : v[i + H];
-      const float keep = upper ? v[i + H] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, H);
-    }
-    TransposeReduce<H>::run(v, lane);
-  }
-};
-template <>
-struct TransposeReduce<1> {
-  static __device__ __forceinline__ void run(float*, int) {}
-};
-
-template <int VEC> struct RawVec;
-template <> struct RawVec<1> { uint16_t r; };
-template <> struct RawVec<2> { uint32_t r; };
-template <> struct RawVec<4> { uint2 r; };
-
-template <int VEC>
-__device__ __forceinline__ void load_row(const bf16* p, RawVec<VEC>& raw);
-template <> __device__ __forceinline__ void load_row<1>(const bf16* p, RawVec<1>& raw) { raw.r = ld_stream_u16(p); }
-template <> __device__ __forceinline__ void load_row<2>(const bf16* p, RawVec<2>& raw) { raw.r = ld_stream_u32(p); }
-template <> __device__ __forceinline__ void load_row<4>(const bf16* p, RawVec<4>& raw) { raw.r = ld_stream_v2(p); }
-
-template <int VEC>
-__device__ __forceinline__ void unpack(const RawVec<VEC>& raw, float* f);
-template <> __device__ __forceinline__ void unpack<1>(const RawVec<1>& raw, float* f) {
-  f[0] = __uint_as_float((uint32_t)raw.r << 16);
-}
-template <> __device__ __forceinline__ void unpack<2>(const RawVec<2>& raw, float* f) {
-  f[0] = bf16_lo(raw.r); f[1] = bf16_hi(raw.r);
-}
-template <> __device__ __forceinline__ void unpack<4>(const RawVec<4>& raw, float* f) {
-  f[0] = bf16_lo(raw.r.x); f[1] = bf16_hi(raw.r.x); f[2] = bf16_lo(raw.r.y); f[3] = bf16_hi(raw.r.y);
-}
-
 constexpr int kWarps = 4;
+constexpr int kTile = 32;          // tokens per tile
+constexpr int kStages = 3;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000ll) __trap();      // never hang the GPU on a protocol bug
+  }
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void mma_bf16(float* d, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
+  uint32_t d;
+  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
+}
+
+template <int D>
+constexpr size_t attn_smem_bytes() {
+  return (size_t)kWarps * kStages * 2 * kTile * D * 2      // K + V^T rings
+         + (size_t)kWarps * 8 * D * 4                      // per-warp O^T for the merge
+         + (size_t)kWarps * 8 * 2 * 4                      // per-warp (m, l)
+         + (size_t)kWarps * kStages * 8 + 128;             // mbarriers + alignment slack
+}
 
 template <int D, int G>
-__global__ void __launch_bounds__(kWarps * 32) attn_decode_kernel(
+__global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
     const bf16* __restrict__ q, KvLayout kv, const int* __restrict__ seq_lens, int S, int nq,
     float* __restrict__ part_o, float* __restrict__ part_ml, int n_splits, float scale_log2) {
-  constexpr int VEC = D / 32;
-  constexpr int TB = 32 / G;
+  static_assert(G >= 1 && G <= 8 && (D == 32 || D == 64 || D == 128), "unsupported shape");
+  constexpr int KSTEP_PAIRS = D / 32;         // 16-byte chunks per thread per K row = pairs of k-steps
+  constexpr int MT_O = D / 16;                // m-tiles of O^T
+  constexpr uint32_t kBlockBytes = kTile * D * 2;
+  constexpr bool kSwizzle = D >= 64;
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = lane >> 2, c = lane & 3;
   const int split = blockIdx.x, kvh = blockIdx.y, t = blockIdx.z;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = t / S;
   const int ctx = seq_lens[b] + (t - b * S) + 1;
-  const int ps = kv.page_size;
-  const int n_pages = (ctx + ps - 1) / ps;
-  const int pages_per_split = (n_pages + n_splits - 1) / n_splits;
-  const int tok_begin = split * pages_per_split * ps;
-  const int tok_end = min(ctx, tok_begin + pages_per_split * ps);
+  const int n_tiles = (ctx + kTile - 1) / kTile;
+  const int tiles_per_split = (n_tiles + n_splits - 1) / n_splits;
+  const int tile_begin = split * tiles_per_split;
+  const int tile_end = min(n_tiles, tile_begin + tiles_per_split);
+  const int my_tiles = (tile_end - tile_begin - warp + kWarps - 1) / kWarps;    // may be <= 0
+
+  uint8_t* ring = smem;                                                          // [warp][stage][K | V^T]
+  float* sm_o = reinterpret_cast<float*>(smem + (size_t)kWarps * kStages * 2 * kBlockBytes);   // [warp][8][D]
+  float* sm_ml = sm_o + kWarps * 8 * D;                                          // [warp][8][2]
+  const uint32_t bars = smem_u32(sm_ml + kWarps * 8 * 2);                        // [warp][stage]
+  const uint32_t my_ring = smem_u32(ring) + (uint32_t)warp * kStages * 2 * kBlockBytes;
+  const uint32_t my_bars = bars + (uint32_t)warp * kStages * 8;
+
+  if (lane == 0) {
+    for (int s = 0; s < kStages; ++s) mbar_init(my_bars + 8u * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+
   const int* table = kv.page_table + (int64_t)b * kv.pages_per_seq;
-  const int64_t head_stride = (int64_t)ps * D;                       // one (page, K|V, head) block
+  const int ps = kv.page_size;
+  const int64_t head_stride = (int64_t)ps * D;                          // elements per (page, K|V, head) block
   const int64_t page_stride = 2 * (int64_t)kv.kv_local * head_stride;
+  auto issue = [&](int i) {                                             // lane 0 only
+    const int tile = tile_begin + warp + i * kWarps;
+    const int tok0 = tile * kTile;
+    const int page = table[tok0 / ps];
+    const int sub = (tok0 % ps) / kTile;                                // 32-token sub-block inside the page
+    const bf16* kp = kv.base + (int64_t)page * page_stride + (int64_t)kvh * head_stride + (int64_t)sub * kTile * D;
+    const bf16* vp = kp + (int64_t)kv.kv_local * head_stride;
+    const int s = i % kStages;
+    const uint32_t bar = my_bars + 8u * s;
+    const uint32_t dst = my_ring + (uint32_t)s * 2 * kBlockBytes;
+    mbar_expect_tx(bar, 2 * kBlockBytes);
+    bulk_copy_g2s(dst, kp, kBlockBytes, bar);
+    bulk_copy_g2s(dst + kBlockBytes, vp, kBlockBytes, bar);
+  };
+  if (lane == 0)
+    for (int i = 0; i < min(kStages, my_tiles); ++i) issue(i);
 
-  float qr[G][VEC];
+  // Q as B fragments: head r (< G), the same d-permutation as the K chunks (chunk c of every 64 bytes)
+  uint32_t qb[KSTEP_PAIRS][4];
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
-    RawVec<VEC> raw;
-    load_row<VEC>(q + ((int64_t)t * nq + kvh * G + g) * D + lane * VEC, raw);
-    unpack<VEC>(raw, qr[g]);
-#pragma unroll
-    for (int v = 0; v < VEC; ++v) qr[g][v] *= scale_log2;
+  for (int j = 0; j < KSTEP_PAIRS; ++j) {
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (r < G) v = *reinterpret_cast<const uint4*>(q + ((int64_t)t * nq + kvh * G + r) * D + c * 8 + 32 * j);
+    qb[j][0] = v.x; qb[j][1] = v.y; qb[j][2] = v.z; qb[j][3] = v.w;
   }
-  float o[G][VEC];
-#pragma unroll
-  for (int g = 0; g < G; ++g)
-#pragma unroll
-    for (int v = 0; v < VEC; ++v) o[g][v] = 0.f;
-  float m = -INFINITY, l = 0.f;
 
-  for (int base = tok_begin + warp * TB; base < tok_end; base += kWarps * TB) {
-    RawVec<VEC> kraw[TB], vraw[TB];
+  float oacc[MT_O][4];
 #pragma unroll
-    for (int j = 0; j < TB; ++j) {
-      const int tok = base + j;
-      if (tok < tok_end) {
-        const int page = table[tok / ps];
-        const bf16* kp = kv.base + (int64_t)page * page_stride + (int64_t)kvh * head_stride +
-                         (int64_t)(tok % ps) * D + lane * VEC;
-        load_row<VEC>(kp, kraw[j]);
-        load_row<VEC>(kp + (int64_t)kv.kv_local * head_stride, vraw[j]);
-      } else {
-        kraw[j] = RawVec<VEC>{};
-        vraw[j] = RawVec<VEC>{};
+  for (int mo = 0; mo < MT_O; ++mo)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) oacc[mo][e] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};      // heads 2c, 2c+1
+
+  for (int i = 0; i < my_tiles; ++i) {
+    const int s = i % kStages;
+    mbar_wait(my_bars + 8u * s, (uint32_t)(i / kStages) & 1u);
+    const uint32_t k_s = my_ring + (uint32_t)s * 2 * kBlockBytes;
+    const uint32_t v_s = k_s + kBlockBytes;
+    const int tok0 = (tile_begin + warp + i * kWarps) * kTile;
+
+    // ---- S^T = K . Q^T : 2 m-tiles of 16 token rows; row r of m-tile mt is token 8*(r>>1)+4*mt+(r&1) (+2 for r+8)
+    float sacc[2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) sacc[mt][e] = 0.f;
+      const int ta = 8 * (r >> 1) + 4 * mt + (r & 1), tb = ta + 2;
+      const uint32_t swz = kSwizzle ? (uint32_t)((ta & 1) << 2) : 0u;   // ta and tb have the same parity
+#pragma unroll
+      for (int j = 0; j < KSTEP_PAIRS; ++j) {
+        const uint32_t chunk = ((uint32_t)(c + 4 * j)) ^ swz;
+        const uint4 x = lds128(k_s + (uint32_t)ta * (D * 2) + chunk * 16);
+        const uint4 y = lds128(k_s + (uint32_t)tb * (D * 2) + chunk * 16);
+        mma_bf16(sacc[mt], x.x, y.x, x.y, y.y, qb[j][0], qb[j][1]);
+        mma_bf16(sacc[mt], x.z, y.z, x.w, y.w, qb[j][2], qb[j][3]);
       }
     }
-    float acc[32];
+    // ---- online softmax over this tile (columns = heads 2c, 2c+1)
+    float tmax[2] = {-INFINITY, -INFINITY};
 #pragma unroll
-    for (int j = 0; j < TB; ++j) {
-      float kf[VEC];
-      unpack<VEC>(kraw[j], kf);
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        float a = 0.f;
-#pragma unroll
-        for (int v = 0; v < VEC; ++v) a += qr[g][v] * kf[v];
-        acc[j * G + g] = a;
-      }
-    }
-    TransposeReduce<32>::run(acc, lane);
-    const bool mine_valid = (base + lane / G) < tok_end;
-    const float s = mine_valid ? acc[0] : -INFINITY;
-    float mx = s;
-#pragma unroll
-    for (int off = G; off < 32; off <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    const float m_new = fmaxf(m, mx);                     // finite: token `base` is valid for every head
-    const float corr = exp2f(m - m_new);                  // m = -inf on the first batch -> 0
-    const float p = mine_valid ? exp2f(s - m_new) : 0.f;
-    l = l * corr + p;
-    m = m_new;
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const float cg = __shfl_sync(0xffffffffu, corr, g);   // lane g owns head g
-#pragma unroll
-      for (int v = 0; v < VEC; ++v) o[g][v] *= cg;
+    for (int mt = 0; mt < 2; ++mt) {
+      const int ta = tok0 + 8 * (r >> 1) + 4 * mt + (r & 1);
+      const bool va = ta < ctx, vb = (ta + 2) < ctx;
+      sacc[mt][0] = va ? sacc[mt][0] * scale_log2 : -INFINITY;
+      sacc[mt][1] = va ? sacc[mt][1] * scale_log2 : -INFINITY;
+      sacc[mt][2] = vb ? sacc[mt][2] * scale_log2 : -INFINITY;
+      sacc[mt][3] = vb ? sacc[mt][3] * scale_log2 : -INFINITY;
+      tmax[0] = fmaxf(tmax[0], fmaxf(sacc[mt][0], sacc[mt][2]));
+      tmax[1] = fmaxf(tmax[1], fmaxf(sacc[mt][1], sacc[mt][3]));
     }
 #pragma unroll
-    for (int j = 0; j < TB; ++j) {
-      float vf[VEC];
-      unpack<VEC>(vraw[j], vf);
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const float pj = __shfl_sync(0xffffffffu, p, j * G + g);
-#pragma unroll
-        for (int v = 0; v < VEC; ++v) o[g][v] += pj * vf[v];
-      }
+    for (int off = 4; off < 32; off <<= 1) {
+      tmax[0] = fmaxf(tmax[0], __shfl_xor_sync(0xffffffffu, tmax[0], off));
+      tmax[1] = fmaxf(tmax[1], __shfl_xor_sync(0xffffffffu, tmax[1], off));
     }
+    float corr[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const float m_new = fmaxf(m_run[e], tmax[e]);     // finite: every tile in range has a valid token
+      corr[e] = exp2f(m_run[e] - m_new);
+      m_run[e] = m_new;
+    }
+    uint32_t pb[2][2];
+    float psum[2] = {0.f, 0.f};
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      const float p0 = exp2f(sacc[mt][0] - m_run[0]), p1 = exp2f(sacc[mt][1] - m_run[1]);
+      const float p2 = exp2f(sacc[mt][2] - m_run[0]), p3 = exp2f(sacc[mt][3] - m_run[1]);
+      psum[0] += p0 + p2;
+      psum[1] += p1 + p3;
+      pb[mt][0] = movmatrix_trans(pack_bf16(p0, p1));   // rows r      -> B k-slots 2c,2c+1   of k-step mt
+      pb[mt][1] = movmatrix_trans(pack_bf16(p2, p3));   // rows r + 8  -> B k-slots 2c+8,2c+9 of k-step mt
+    }
+    l_run[0] = l_run[0] * corr[0] + psum[0];
+    l_run[1] = l_run[1] * corr[1] + psum[1];
+    // ---- O^T += V^T . P^T : m-tiles over d, 2 k-steps over the 32 tokens
+#pragma unroll
+    for (int mo = 0; mo < MT_O; ++mo) {
+      oacc[mo][0] *= corr[0]; oacc[mo][1] *= corr[1]; oacc[mo][2] *= corr[0]; oacc[mo][3] *= corr[1];
+      const uint4 x = lds128(v_s + (uint32_t)(16 * mo + r) * (kTile * 2) + c * 16);
+      const uint4 y = lds128(v_s + (uint32_t)(16 * mo + r + 8) * (kTile * 2) + c * 16);
+      mma_bf16(oacc[mo], x.x, y.x, x.y, y.y, pb[0][0], pb[0][1]);
+      mma_bf16(oacc[mo], x.z, y.z, x.w, y.w, pb[1][0], pb[1][1]);
+    }
+    __syncwarp();                                        // every lane is done reading stage s
+    if (lane == 0 && i + kStages < my_tiles) issue(i + kStages);
   }
-  // per-head l over the lanes that share the head
-#pragma unroll
-  for (int off = G; off < 32; off <<= 1) l += __shfl_xor_sync(0xffffffffu, l, off);
 
-  __shared__ float sm_m[kWarps][G], sm_l[kWarps][G];
-  __shared__ float sm_o[kWarps][G][D];
-  if (lane < G) { sm_m[warp][lane] = m; sm_l[warp][lane] = l; }
+  // ---- merge the CTA's warps ----
 #pragma unroll
-  for (int g = 0; g < G; ++g)
+  for (int off = 4; off < 32; off <<= 1) {
+    l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], off);
+    l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], off);
+  }
+  if (r == 0) {
+    sm_ml[(warp * 8 + 2 * c) * 2] = m_run[0];     sm_ml[(warp * 8 + 2 * c) * 2 + 1] = l_run[0];
+    sm_ml[(warp * 8 + 2 * c + 1) * 2] = m_run[1]; sm_ml[(warp * 8 + 2 * c + 1) * 2 + 1] = l_run[1];
+  }
 #pragma unroll
-    for (int v = 0; v < VEC; ++v) sm_o[warp][g][lane * VEC + v] = o[g][v];
+  for (int mo = 0; mo < MT_O; ++mo) {
+    float* o0 = sm_o + ((size_t)warp * 8 + 2 * c) * D + 16 * mo + r;
+    o0[0] = oacc[mo][0]; o0[D] = oacc[mo][1]; o0[8] = oacc[mo][2]; o0[D + 8] = oacc[mo][3];
+  }
   __syncthreads();
   for (int idx = threadIdx.x; idx < G * D; idx += kWarps * 32) {
     const int g = idx / D, dd = idx - g * D;
-    float M = sm_m[0][g];
+    float M = -INFINITY;
 #pragma unroll
-    for (int w = 1; w < kWarps; ++w) M = fmaxf(M, sm_m[w][g]);
+    for (int w = 0; w < kWarps; ++w) M = fmaxf(M, sm_ml[(w * 8 + g) * 2]);
     float L = 0.f, O = 0.f;
     if (M > -INFINITY) {
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) {
-        const float f = exp2f(sm_m[w][g] - M);
-        L += sm_l[w][g] * f;
-        O += sm_o[w][g][dd] * f;
+        const float mw = sm_ml[(w * 8 + g) * 2];
+        if (mw > -INFINITY) {
+          const float f = exp2f(mw - M);
+          L += sm_ml[(w * 8 + g) * 2 + 1] * f;
+          O += sm_o[((size_t)w * 8 + g) * D + dd] * f;
+        }
       }
     }
     const int64_t slot = ((int64_t)t * nq + kvh * G + g) * n_splits + split;
@@ -207,10 +288,16 @@ __global__ void attn_combine_kernel(const float* __restrict__ part_o, const floa
 template <int D, int G>
 int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, int T, int nq, float* part_o,
                 float* part_ml, int n_splits, bf16* out, cudaStream_t stream) {
+  static bool attr_done = false;
+  constexpr size_t smem = attn_smem_bytes<D>();
+  if (!attr_done) {
+    BFLY_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done = true;
+  }
   dim3 grid(n_splits, kv.kv_local, T);
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
-  attn_decode_kernel<D, G><<<grid, kWarps * 32, 0, stream>>>(q, kv, seq_lens, S, nq, part_o, part_ml, n_splits,
-                                                            scale_log2);
+  attn_decode_kernel<D, G><<<grid, kWarps * 32, smem, stream>>>(q, kv, seq_lens, S, nq, part_o, part_ml, n_splits,
+                                                               scale_log2);
   BFLY_CUDA(cudaGetLastError());
   attn_combine_kernel<D><<<T * nq, D, 0, stream>>>(part_o, part_ml, n_splits, out);
   BFLY_CUDA(cudaGetLastError());
@@ -220,16 +307,28 @@ int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, i
 
 }  // namespace
 
+// Choose the context split so that (token x kv-head x split) CTAs fill whole waves of SMs (one CTA per
+// SM: the rings take ~200 KB of shared memory) while every CTA keeps at least a few tiles per warp.
 int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count) {
-  const int want = ceil_div(sm_count * 8, std::max(1, T * kv_local));
-  const int cap = std::max(1, max_ctx / 64);
-  return std::max(1, std::min(std::min(want, cap), 64));
+  const int base = std::max(1, T * kv_local);
+  const int tiles = std::max(1, (max_ctx + kTile - 1) / kTile);
+  if (base >= 4 * sm_count) return 1;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int n = 1; n <= 32 && n <= tiles; ++n) {
+    if (n > 1 && tiles / n < 2 * kWarps) break;
+    const double load = (double)base * n / sm_count;
+    const double eff = load / std::ceil(load);
+    if (eff > best_eff + 0.02) { best_eff = eff; best = n; }
+  }
+  return best;
 }
 
 int launch_attn_decode(const bf16* q, KvLayout kv, const int* seq_lens, int S, int T, int nq, float* part_o,
                        float* part_ml, int n_splits, bf16* out, cudaStream_t stream) {
   BFLY_CHECK(T > 0 && T <= 65535 && n_splits >= 1 && kv.kv_local >= 1 && nq % kv.kv_local == 0,
              "attn_decode: bad shape (T<=65535, nq % kv_local == 0)");
+  BFLY_CHECK(kv.page_size % kTile == 0, "attn_decode: page_size must be a multiple of 32");
   const int G = nq / kv.kv_local, D = kv.head_dim;
 #define BFLY_ATTN_CASE(DD, GG) \
   if (D == DD && G == GG) return launch_impl<DD, GG>(q, kv, seq_lens, S, T, nq, part_o, part_ml, n_splits, out, stream)

@@ -2,6 +2,8 @@
 // coalesced accesses, warp-shuffle reductions, fp32 math, bf16 only where the numerics contract
 // stores a GEMM operand or the KV cache.  Each consumer also folds the split-K slices of the GEMM
 // that produced its input (and the bias / residual add), so no separate reduction pass exists.
+#include <algorithm>
+
 #include "kernels.cuh"
 
 namespace bfly {
@@ -50,7 +52,7 @@ int launch_embed(const int* tokens, const bf16* table, const bf16* pos_table, co
 // ---------------------------------------------------------------------------------------------
 // K3: residual += sum(split-K slices) + bias;  out = norm(residual) as the next GEMM's bf16 operand
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) add_norm_kernel(
+__global__ void __launch_bounds__(1024) add_norm_kernel(
     float* __restrict__ residual, const float* __restrict__ partials, int n_partials, int64_t partial_stride,
     const bf16* __restrict__ bias, const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float eps,
     int layer_norm, bf16* __restrict__ out, int h) {
@@ -61,8 +63,19 @@ __global__ void __launch_bounds__(256) add_norm_kernel(
   float sum = 0.f, sumsq = 0.f;
   for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
     float4 v = *reinterpret_cast<const float4*>(res + i);
-    for (int p = 0; p < n_partials; ++p) {
-      const float4 a = *reinterpret_cast<const float4*>(partials + p * partial_stride + (int64_t)row * h + i);
+    const float* pp = partials + (int64_t)row * h + i;
+    // slices are folded in index order, four loads in flight at a time (latency, not bandwidth, bound)
+    int p = 0;
+    for (; p + 4 <= n_partials; p += 4) {
+      const float4 a0 = *reinterpret_cast<const float4*>(pp + (p + 0) * partial_stride);
+      const float4 a1 = *reinterpret_cast<const float4*>(pp + (p + 1) * partial_stride);
+      const float4 a2 = *reinterpret_cast<const float4*>(pp + (p + 2) * partial_stride);
+      const float4 a3 = *reinterpret_cast<const float4*>(pp + (p + 3) * partial_stride);
+      v.x = (((v.x + a0.x) + a1.x) + a2.x) + a3.x; v.y = (((v.y + a0.y) + a1.y) + a2.y) + a3.y;
+      v.z = (((v.z + a0.z) + a1.z) + a2.z) + a3.z; v.w = (((v.w + a0.w) + a1.w) + a2.w) + a3.w;
+    }
+    for (; p < n_partials; ++p) {
+      const float4 a = *reinterpret_cast<const float4*>(pp + p * partial_stride);
       v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
     }
     if (bias != nullptr) {
@@ -113,7 +126,8 @@ int launch_add_norm(float* residual, const float* partials, int n_partials, int6
     BFLY_CUDA(cudaFuncSetAttribute(add_norm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     attr_set = true;
   }
-  add_norm_kernel<<<T, 256, smem, stream>>>(residual, partials, n_partials, partial_stride, bias, gamma, beta,
+  const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
+  add_norm_kernel<<<T, threads, smem, stream>>>(residual, partials, n_partials, partial_stride, bias, gamma, beta,
                                             eps, layer_norm, out, h);
   count_launch();
   BFLY_CUDA(cudaGetLastError());
@@ -159,9 +173,16 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_partials, in
     const int kh = (head - nq) - which * nk;
     const int page = kv.page_table[(int64_t)b * kv.pages_per_seq + pos / kv.page_size];
     const int slot = pos % kv.page_size;
-    bf16* dst = kv.base + ((((int64_t)page * 2 + which) * kv.kv_local + kh) * kv.page_size + slot) * d;
-    dst[i] = __float2bfloat16_rn(x0);
-    dst[i + half] = __float2bfloat16_rn(x1);
+    bf16* blk = kv.base + (((int64_t)page * 2 + which) * kv.kv_local + kh) * kv.page_size * d;
+    if (which == 0) {
+      // K block: [page_size][d] rows; 16-byte chunks XOR-swizzled by token parity (see attn_decode.cu)
+      blk[kv_k_offset(slot, i, d)] = __float2bfloat16_rn(x0);
+      blk[kv_k_offset(slot, i + half, d)] = __float2bfloat16_rn(x1);
+    } else {
+      // V block: transposed per 32-token sub-block, [page_size/32][d][32]
+      blk[kv_v_offset(slot, i, d)] = __float2bfloat16_rn(x0);
+      blk[kv_v_offset(slot, i + half, d)] = __float2bfloat16_rn(x1);
+    }
   }
 }
 

@@ -94,7 +94,7 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   BFLY_CHECK(c.n_heads % c.tp == 0 && c.n_kv_heads % c.tp == 0 && c.n_heads % c.n_kv_heads == 0, "heads vs tp");
   BFLY_CHECK(c.n_experts == 0 ? c.ffn % c.tp == 0 : (c.n_experts % c.tp == 0 && c.n_experts <= 32), "ffn/experts vs tp");
   BFLY_CHECK(c.n_experts == 0 || (c.top_k >= 1 && c.top_k <= c.n_experts), "top_k");
-  BFLY_CHECK(c.page_size >= 8 && (c.page_size & (c.page_size - 1)) == 0, "page_size power of two >= 8");
+  BFLY_CHECK(c.page_size >= 32 && (c.page_size & (c.page_size - 1)) == 0, "page_size power of two >= 32");
   BFLY_CHECK(c.max_batch >= 1 && c.max_ctx >= 1 && c.max_tokens >= c.max_batch, "max_batch/max_ctx/max_tokens");
   BFLY_CHECK(c.rope_theta > 0.f || c.max_pos >= c.max_ctx, "learned positions need max_pos >= max_ctx");
   BFLY_CUDA(cudaSetDevice(device));
@@ -184,6 +184,8 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   for (int64_t i = 0; i < e->n_pages; ++i) table[(size_t)i] = (int)i;
   BFLY_CUDA(cudaMemcpy(e->page_table, table.data(), table.size() * sizeof(int), cudaMemcpyHostToDevice));
   BFLY_CUDA(cudaMemset(e->seq_lens, 0, (size_t)maxB * sizeof(int)));
+  // stale cache slots are multiplied by an exact 0 probability: they must never hold NaN/Inf bits
+  BFLY_CUDA(cudaMemset(e->kv_pages, 0, (size_t)c.n_layers * e->layer_kv_elems * sizeof(bf16)));
   BFLY_CUDA(cudaMemset(e->step_counter, 0, sizeof(int)));
   BFLY_CUDA(cudaMemset(e->cur_tokens, 0, (size_t)maxB * sizeof(int)));
   if (c.rope_theta > 0.f) {

@@ -19,6 +19,21 @@ struct KvLayout {
   int head_dim;
 };
 
+// Element offsets inside one (page, K|V, head) block of page_size*head_dim elements.
+//   K: row-major [slot][d]; for d >= 64 the 16-byte chunks of a row are XOR-swizzled by token parity
+//      (chunk ^ 4*(slot&1)) so the tensor-core fragment reads in attn_decode.cu are bank-conflict free
+//      after a plain linear bulk copy into shared memory.
+//   V: transposed per 32-token sub-block, [slot/32][d][slot%32], so a tile of V^T is contiguous and
+//      token-major fragments are 16-byte reads.
+__host__ __device__ inline int64_t kv_k_offset(int slot, int dd, int d) {
+  int chunk = dd >> 3;
+  if (d >= 64) chunk ^= (slot & 1) << 2;
+  return (int64_t)slot * d + (chunk << 3) + (dd & 7);
+}
+__host__ __device__ inline int64_t kv_v_offset(int slot, int dd, int d) {
+  return (int64_t)(slot >> 5) * d * 32 + (int64_t)dd * 32 + (slot & 31);
+}
+
 enum ActMode : int { ACT_SWIGLU = 0, ACT_GELU_TANH = 1 };
 
 // Token t = b*S + s of a forward over S new tokens per sequence sits at position seq_lens[b] + s.

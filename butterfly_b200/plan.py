@@ -125,8 +125,8 @@ def make_plan(cfg: ModelConfig, tp: int, page_size: int = DEFAULT_PAGE_SIZE) -> 
             raise PlanError(f"{cfg.name}: n_experts={cfg.n_experts} not divisible by tp={tp}")
     elif cfg.ffn % tp:
         raise PlanError(f"{cfg.name}: ffn={cfg.ffn} not divisible by tp={tp}")
-    if page_size < 8 or page_size & (page_size - 1):
-        raise PlanError("page_size must be a power of two >= 8")
+    if page_size < 32 or page_size & (page_size - 1):
+        raise PlanError("page_size must be a power of two >= 32 (attention streams 32-token tiles)")
     if (cfg.head_dim * 2) % 16 or cfg.hidden % 8:
         raise PlanError("head_dim and hidden must keep rows 16-byte aligned in bf16")
 
