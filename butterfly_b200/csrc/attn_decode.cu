@@ -83,7 +83,8 @@ constexpr size_t attn_smem_bytes() {
 template <int D, int G>
 __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
     const bf16* __restrict__ q, KvLayout kv, const int* __restrict__ seq_lens, int S, int nq,
-    float* __restrict__ part_o, float* __restrict__ part_ml, int n_splits, float scale_log2) {
+    float* __restrict__ part_o, float* __restrict__ part_ml, int n_splits, float scale_log2,
+    bf16* __restrict__ out_direct) {
   static_assert(G >= 1 && G <= 8 && (D == 32 || D == 64 || D == 128), "unsupported shape");
   constexpr int KSTEP_PAIRS = D / 32;         // 16-byte chunks per thread per K row = pairs of k-steps
   constexpr int MT_O = D / 16;                // m-tiles of O^T
@@ -91,6 +92,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
   constexpr bool kSwizzle = D >= 64;
 
   extern __shared__ __align__(128) uint8_t smem[];
+  pdl_trigger();
+  pdl_wait();                     // seq_lens, q and the cache are written by earlier kernels of the step
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = lane >> 2, c = lane & 3;
   const int split = blockIdx.x, kvh = blockIdx.y, t = blockIdx.z;
@@ -260,15 +263,21 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
         }
       }
     }
-    const int64_t slot = ((int64_t)t * nq + kvh * G + g) * n_splits + split;
-    part_o[slot * D + dd] = O;
-    if (dd == 0) { part_ml[slot * 2] = M; part_ml[slot * 2 + 1] = L; }
+    if (out_direct != nullptr) {          // single split: this CTA saw the whole context
+      out_direct[((int64_t)t * nq + kvh * G + g) * D + dd] = __float2bfloat16_rn(O / L);
+    } else {
+      const int64_t slot = ((int64_t)t * nq + kvh * G + g) * n_splits + split;
+      part_o[slot * D + dd] = O;
+      if (dd == 0) { part_ml[slot * 2] = M; part_ml[slot * 2 + 1] = L; }
+    }
   }
 }
 
 template <int D>
 __global__ void attn_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                                     int n_splits, bf16* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t th = blockIdx.x;                 // t * nq + head
   const int dd = threadIdx.x;
   float M = -INFINITY;
@@ -296,12 +305,13 @@ int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, i
   }
   dim3 grid(n_splits, kv.kv_local, T);
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
-  attn_decode_kernel<D, G><<<grid, kWarps * 32, smem, stream>>>(q, kv, seq_lens, S, nq, part_o, part_ml, n_splits,
-                                                               scale_log2);
-  BFLY_CUDA(cudaGetLastError());
-  attn_combine_kernel<D><<<T * nq, D, 0, stream>>>(part_o, part_ml, n_splits, out);
-  BFLY_CUDA(cudaGetLastError());
-  count_launch(2);
+  BFLY_CUDA(launch_pdl(attn_decode_kernel<D, G>, grid, dim3(kWarps * 32), smem, stream, q, kv, seq_lens, S, nq, part_o,
+                       part_ml, n_splits, scale_log2, n_splits == 1 ? out : nullptr));
+  count_launch();
+  if (n_splits > 1) {
+    BFLY_CUDA(launch_pdl(attn_combine_kernel<D>, dim3(T * nq), dim3(D), 0, stream, part_o, part_ml, n_splits, out));
+    count_launch();
+  }
   return BFLY_OK;
 }
 
@@ -312,16 +322,12 @@ int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, i
 int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count) {
   const int base = std::max(1, T * kv_local);
   const int tiles = std::max(1, (max_ctx + kTile - 1) / kTile);
-  if (base >= 4 * sm_count) return 1;
-  int best = 1;
-  double best_eff = 0.0;
-  for (int n = 1; n <= 32 && n <= tiles; ++n) {
-    if (n > 1 && tiles / n < 2 * kWarps) break;
-    const double load = (double)base * n / sm_count;
-    const double eff = load / std::ceil(load);
-    if (eff > best_eff + 0.02) { best_eff = eff; best = n; }
-  }
-  return best;
+  // Measured on B200 (tools/tune_kernels.py attn): splitting only pays while there are fewer CTAs than
+  // SMs -- each extra split adds a ring ramp-up and a slice for the combine kernel.  Take the smallest
+  // split that gives every SM a CTA, keeping at least two tiles per warp.
+  int n = 1;
+  while (base * n < sm_count && n < 32 && tiles / (n + 1) >= 2 * kWarps) ++n;
+  return n;
 }
 
 int launch_attn_decode(const bf16* q, KvLayout kv, const int* seq_lens, int S, int T, int nq, float* part_o,

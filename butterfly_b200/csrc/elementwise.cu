@@ -15,6 +15,8 @@ __global__ void embed_kernel(const int* __restrict__ tokens, const bf16* __restr
                              const bf16* __restrict__ pos_table, const int* __restrict__ seq_lens, int S,
                              float* __restrict__ residual, int h, int vocab, unsigned long long* argmax_keys,
                              int n_keys, int* history, const int* step_counter) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x;
   int tok = tokens[t];
   if (history != nullptr && threadIdx.x == 0) history[(int64_t)(*step_counter) * gridDim.x + t] = tok;
@@ -42,8 +44,8 @@ int launch_embed(const int* tokens, const bf16* table, const bf16* pos_table, co
                  float* residual, int T, int h, int vocab, unsigned long long* argmax_keys, int n_keys,
                  int* history, const int* step_counter, cudaStream_t stream) {
   BFLY_CHECK(T > 0 && h % 8 == 0 && S > 0, "embed: T>0, S>0, h%8==0");
-  embed_kernel<<<T, 128, 0, stream>>>(tokens, table, pos_table, seq_lens, S, residual, h, vocab, argmax_keys,
-                                      n_keys, history, step_counter);
+  BFLY_CUDA(launch_pdl(embed_kernel, dim3(T), dim3(128), 0, stream, tokens, table, pos_table, seq_lens, S, residual, h, vocab, argmax_keys,
+                                      n_keys, history, step_counter));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -56,6 +58,8 @@ __global__ void __launch_bounds__(1024) add_norm_kernel(
     float* __restrict__ residual, const float* __restrict__ partials, int n_partials, int64_t partial_stride,
     const bf16* __restrict__ bias, const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float eps,
     int layer_norm, bf16* __restrict__ out, int h) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) float srow[];
   __shared__ float red[32];
   const int row = blockIdx.x;
@@ -127,8 +131,8 @@ int launch_add_norm(float* residual, const float* partials, int n_partials, int6
     attr_set = true;
   }
   const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
-  add_norm_kernel<<<T, threads, smem, stream>>>(residual, partials, n_partials, partial_stride, bias, gamma, beta,
-                                            eps, layer_norm, out, h);
+  BFLY_CUDA(launch_pdl(add_norm_kernel, dim3(T), dim3(threads), smem, stream, residual, partials, n_partials, partial_stride, bias, gamma, beta,
+                                            eps, layer_norm, out, h));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -142,6 +146,8 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_partials, in
                                const bf16* __restrict__ bias, const float2* __restrict__ rope_table,
                                const int* __restrict__ seq_lens, int S, int nq, int nk, bf16* __restrict__ q_out,
                                KvLayout kv) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x, head = blockIdx.y, i = threadIdx.x;
   const int d = kv.head_dim, half = d >> 1;
   const int ld = (nq + 2 * nk) * d;
@@ -192,8 +198,8 @@ int launch_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, con
   BFLY_CHECK(T > 0 && n_partials >= 1 && kv.head_dim % 2 == 0 && kv.head_dim <= 2048, "rope_kv: bad shape");
   BFLY_CHECK(nk == kv.kv_local, "rope_kv: nk must equal the cache's kv heads");
   dim3 grid(T, nq + 2 * nk);
-  rope_kv_kernel<<<grid, kv.head_dim / 2, 0, stream>>>(qkv, n_partials, partial_stride, bias, rope_table, seq_lens,
-                                                      S, nq, nk, q_out, kv);
+  BFLY_CUDA(launch_pdl(rope_kv_kernel, dim3(grid), dim3(kv.head_dim / 2), 0, stream, qkv, n_partials, partial_stride, bias, rope_table, seq_lens,
+                                                      S, nq, nk, q_out, kv));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -210,6 +216,8 @@ __device__ __forceinline__ float gelu_tanh_f(float x) {
 __global__ void act_kernel(const float* __restrict__ in, int n_partials, int64_t partial_stride,
                            const bf16* __restrict__ bias, int mode, int n_blocks, int f_block,
                            const float* __restrict__ route_w, bf16* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.y;
   const int f_out = n_blocks * f_block;
   const int j = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -252,7 +260,7 @@ int launch_act(const float* in, int n_partials, int64_t partial_stride, const bf
   BFLY_CHECK(T > 0 && n_partials >= 1 && n_blocks >= 1 && f_block % 4 == 0, "act: bad shape (f_block%4==0)");
   const int f_out = n_blocks * f_block;
   dim3 grid(ceil_div(f_out / 4, 256), T);
-  act_kernel<<<grid, 256, 0, stream>>>(in, n_partials, partial_stride, bias, mode, n_blocks, f_block, route_w, out);
+  BFLY_CUDA(launch_pdl(act_kernel, dim3(grid), dim3(256), 0, stream, in, n_partials, partial_stride, bias, mode, n_blocks, f_block, route_w, out));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -274,6 +282,8 @@ constexpr int LM_CHUNK = 2048;
 __global__ void __launch_bounds__(256) lm_finalize_kernel(
     const float* __restrict__ partials, int n_partials, int64_t partial_stride, int v_local, int v0,
     float* __restrict__ logits, int64_t logits_ld, unsigned long long* __restrict__ keys) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.y;
   const int begin = blockIdx.x * LM_CHUNK, end = min(v_local, begin + LM_CHUNK);
   unsigned long long best = 0ull;
@@ -302,8 +312,8 @@ int launch_lm_finalize(const float* partials, int n_partials, int64_t partial_st
                        int v0, float* logits, int64_t logits_ld, unsigned long long* keys, cudaStream_t stream) {
   BFLY_CHECK(T > 0 && v_local > 0 && n_partials >= 1 && keys != nullptr, "lm_finalize: bad shape");
   dim3 grid(ceil_div(v_local, LM_CHUNK), T);
-  lm_finalize_kernel<<<grid, 256, 0, stream>>>(partials, n_partials, partial_stride, v_local, v0, logits,
-                                              logits_ld, keys);
+  BFLY_CUDA(launch_pdl(lm_finalize_kernel, dim3(grid), dim3(256), 0, stream, partials, n_partials, partial_stride, v_local, v0, logits,
+                                              logits_ld, keys));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -311,6 +321,8 @@ int launch_lm_finalize(const float* partials, int n_partials, int64_t partial_st
 
 __global__ void pick_tokens_kernel(const unsigned long long* __restrict__ keys, int n_ranks, int pitch, int T,
                                    int* __restrict__ tokens_out) {
+  pdl_trigger();
+  pdl_wait();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= T) return;
   unsigned long long best = 0ull;
@@ -325,20 +337,22 @@ __global__ void pick_tokens_kernel(const unsigned long long* __restrict__ keys, 
 int launch_pick_tokens_pitched(const unsigned long long* keys, int n_ranks, int pitch, int T, int* tokens_out,
                                cudaStream_t stream) {
   BFLY_CHECK(T > 0 && n_ranks >= 1 && pitch >= T, "pick_tokens: bad shape");
-  pick_tokens_kernel<<<ceil_div(T, 128), 128, 0, stream>>>(keys, n_ranks, pitch, T, tokens_out);
+  BFLY_CUDA(launch_pdl(pick_tokens_kernel, dim3(ceil_div(T, 128)), dim3(128), 0, stream, keys, n_ranks, pitch, T, tokens_out));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
 }
 
 __global__ void advance_kernel(int* seq_lens, int B, int S, int* step_counter) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < B) seq_lens[b] += S;
   if (b == 0 && step_counter != nullptr) *step_counter += 1;
 }
 
 int launch_advance(int* seq_lens, int B, int S, int* step_counter, cudaStream_t stream) {
-  advance_kernel<<<ceil_div(B, 128), 128, 0, stream>>>(seq_lens, B, S, step_counter);
+  BFLY_CUDA(launch_pdl(advance_kernel, dim3(ceil_div(B, 128)), dim3(128), 0, stream, seq_lens, B, S, step_counter));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -351,6 +365,8 @@ int launch_advance(int* seq_lens, int B, int S, int* step_counter, cudaStream_t 
 __global__ void moe_router_kernel(const bf16* __restrict__ xn, const bf16* __restrict__ router, int h,
                                   int n_experts, int top_k, int first_local, int n_local,
                                   float* __restrict__ route_w) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float logit[32];
   const int t = blockIdx.x, e = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bf16* x = xn + (int64_t)t * h;
@@ -391,7 +407,7 @@ int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_ex
                       int first_local, int n_local, float* route_w, cudaStream_t stream) {
   BFLY_CHECK(T > 0 && h % 8 == 0 && n_experts >= 1 && n_experts <= 32 && top_k >= 1 && top_k <= n_experts,
              "moe_router: bad shape");
-  moe_router_kernel<<<T, 32 * n_experts, 0, stream>>>(xn, router, h, n_experts, top_k, first_local, n_local, route_w);
+  BFLY_CUDA(launch_pdl(moe_router_kernel, dim3(T), dim3(32 * n_experts), 0, stream, xn, router, h, n_experts, top_k, first_local, n_local, route_w));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -402,6 +418,8 @@ int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_ex
 // ---------------------------------------------------------------------------------------------
 __global__ void reduce_partials_kernel(const float* __restrict__ partials, int n_partials, int64_t partial_stride,
                                        float* __restrict__ out, int64_t count4) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= count4) return;
   float4 v = reinterpret_cast<const float4*>(partials)[i];
@@ -416,7 +434,7 @@ int launch_reduce_partials(const float* partials, int n_partials, int64_t partia
                            int64_t count, cudaStream_t stream) {
   BFLY_CHECK(count > 0 && count % 4 == 0 && n_partials >= 1 && partial_stride % 4 == 0, "reduce_partials: bad shape");
   const int64_t c4 = count / 4;
-  reduce_partials_kernel<<<(unsigned)ceil_div64(c4, 256), 256, 0, stream>>>(partials, n_partials, partial_stride, out, c4);
+  BFLY_CUDA(launch_pdl(reduce_partials_kernel, dim3((unsigned)ceil_div64(c4, 256)), dim3(256), 0, stream, partials, n_partials, partial_stride, out, c4));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;

@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
   const int kb_end = (int)((int64_t)nkb_total * (blockIdx.z + 1) / args.splits);
   const int nkb = kb_end - kb_begin;
 
+  pdl_trigger();
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
@@ -152,7 +153,17 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
   if (warp == 0) {
     if (lane == 0) {
       const uint32_t tx = kABytes + b_bytes;
-      for (int i = 0; i < nkb; ++i) {
+      // Weights never depend on earlier kernels: fill the whole ring with weight tiles BEFORE waiting
+      // for the predecessor (programmatic dependent launch), then add the activation tiles.
+      const int pre = min(stages, nkb);
+      for (int i = 0; i < pre; ++i) {
+        mbar_expect_tx(full_bar(i), tx);
+        tma_load_2d(a_base + (uint32_t)i * kABytes, &tmap_w, full_bar(i), (kb_begin + i) * BK, m0, kEvictFirst);
+      }
+      pdl_wait();
+      for (int i = 0; i < pre; ++i)
+        tma_load_2d(b_base + (uint32_t)i * b_bytes, &tmap_x, full_bar(i), (kb_begin + i) * BK, n0, kEvictLast);
+      for (int i = pre; i < nkb; ++i) {
         const int s = i % stages;
         const uint32_t ph = (uint32_t)(i / stages) & 1u;
         mbar_wait(empty_bar(s), ph ^ 1u);
@@ -184,6 +195,7 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
       umma_commit(tmem_full_bar);          // accumulator complete
     }
   } else {
+    pdl_wait();      // outputs alias scratch that an earlier consumer kernel may still be reading
     mbar_wait(tmem_full_bar, 0);
     tcgen05_fence_after();
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
@@ -314,9 +326,8 @@ int launch_gemm(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& plan,
   a.tmem_cols = cols;
   a.out_f32 = out_f32; a.out_bf16 = out_bf16; a.split_stride = split_stride; a.ldc = ldc;
   dim3 grid(ceil_div(plan.M, BM), ceil_div(plan.N, plan.bn), plan.splits);
-  gemm_tn_kernel<<<grid, kThreads, smem, stream>>>(mw, mx, a);
+  BFLY_CUDA(launch_pdl(gemm_tn_kernel, grid, dim3(kThreads), smem, stream, mw, mx, a));
   count_launch();
-  BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
 }
 
