@@ -121,6 +121,18 @@ int bfly_k_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, con
 int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
                        int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int T, int nq,
                        float* part_o, float* part_ml, int n_splits, void* out_bf16, void* stream);
+/* Same computation as bfly_k_attn_decode for callers that cannot supply or allocate the split-context
+ * scratch (the host application's pool owns all of the GPU's memory, cudaMalloc is banned from the
+ * hot path, or a binding forwards only inputs and outputs).  The scratch is a fixed 4 MiB array inside
+ * the library, present on every GPU that loads it until the process exits.  Needs
+ * T*nq*n_splits*(head_dim+2) floats <= 1,048,576, otherwise BFLY_EINVAL and nothing runs.  Allocates
+ * nothing.  The first call on a device resolves the array's address: make it at start-up, before any
+ * stream capture on that device.  Calls on one device share the array (contents of the previous call
+ * remain; nothing needs zeroing); calls that overlap on the GPU race -- serialise them.
+ * No counterpart in the reference: this entry point is an addition of this library. */
+int bfly_k_attn_decode_static(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table,
+                              int pages_per_seq, int page_size, int kv_local, int head_dim, const int32_t* seq_lens,
+                              int S, int T, int nq, int n_splits, void* out_bf16, void* stream);
 int bfly_k_act(const float* in, int n_partials, int64_t partial_stride, const void* bias_bf16, int mode,
                int n_blocks, int f_block, const float* route_w, void* out_bf16, int T, void* stream);
 int bfly_k_lm_finalize(const float* partials, int n_partials, int64_t partial_stride, int T, int v_local, int v0,
