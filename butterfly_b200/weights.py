@@ -27,6 +27,8 @@ create its shard directly in HBM without any host copy of the full model.
 from __future__ import annotations
 
 import math
+import os
+from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -62,10 +64,11 @@ def synth_block(key: int, ncols_full: int, r0: int, r1: int, c0: int, c1: int,
     if out.numel() == 0:
         return out
     cols = np.arange(c0, c1, dtype=np.uint64)[None, :]
-    step = max(1, (1 << 22) // max(1, c1 - c0))
-    with np.errstate(over="ignore"):
-        for a in range(r0, r1, step):
-            b = min(r1, a + step)
+    step = max(1, (1 << 21) // max(1, c1 - c0))
+
+    def fill(a: int):
+        b = min(r1, a + step)
+        with np.errstate(over="ignore"):
             rows = np.arange(a, b, dtype=np.uint64)[:, None]
             z = np.uint64(key) + (rows * np.uint64(ncols_full) + cols) * np.uint64(_GOLDEN)
             z = (z ^ (z >> np.uint64(30))) * np.uint64(_M1)
@@ -76,7 +79,15 @@ def synth_block(key: int, ncols_full: int, r0: int, r1: int, c0: int, c1: int,
             v = (s.astype(np.int64) - 131070).astype(np.float32) * scale
             if offset != 0.0:
                 v = v + np.float32(offset)
-            out[a - r0:b - r0] = torch.from_numpy(v).to(torch.bfloat16)
+        out[a - r0:b - r0] = torch.from_numpy(v).to(torch.bfloat16)
+
+    starts = list(range(r0, r1, step))
+    if len(starts) > 4:                        # numpy releases the GIL inside its ufuncs
+        with ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1)) as ex:
+            list(ex.map(fill, starts))
+    else:
+        for a in starts:
+            fill(a)
     return out
 
 

@@ -7,7 +7,7 @@ pipeline -- BASELINE.md "Parity protocol"); every disagreement is reported with 
 import pytest
 import torch
 
-from butterfly_b200 import (LLAMA3_8B, SyntheticSource, make_plan, shard_weights, synthetic_tokens, tiny)
+from butterfly_b200 import (GPT2_SMALL, LLAMA3_8B, LLAMA3_70B, MIXTRAL_8X7B, SyntheticSource, make_plan, shard_weights, synthetic_tokens, tiny)
 from oracle import OracleModel, ops
 
 pytestmark = pytest.mark.gpu
@@ -107,6 +107,23 @@ def test_free_running_greedy_matches_teacher_forced(cuda):
 def test_llama3_8b_width_shallow_parity(cuda):
     """Full Llama-3-8B width (h=4096, 32/8 heads, f=14336, V=128256), depth 2, B=4, prefill 48 + 4 steps."""
     _run_parity(LLAMA3_8B.with_layers(2), B=4, S=48, n_steps=4, device_synth=True)
+
+
+def test_gpt2_small_full_parity(cuda):
+    """BASELINE.json configs[0] shape: GPT-2 small (124M, all 12 layers, V=50257), B=1 (and 2), ctx 64,
+    32 greedy steps teacher-forced (the TP=2 variant of this config is tests/test_gpu_tp.py)."""
+    _run_parity(GPT2_SMALL, B=2, S=64, n_steps=32, device_synth=True)
+
+
+def test_llama3_70b_width_shallow_parity(cuda):
+    """Llama-3-70B width (h=8192, 64/8 heads -> GQA group 8, f=28672), depth 1 (fp32 oracle of the full
+    model would need 282 GB of host RAM)."""
+    _run_parity(LLAMA3_70B.with_layers(1), B=2, S=33, n_steps=2, device_synth=True)
+
+
+def test_mixtral_8x7b_width_shallow_parity(cuda):
+    """Mixtral-8x7B width (8 experts of f=14336, top-2, V=32000), depth 1."""
+    _run_parity(MIXTRAL_8X7B.with_layers(1), B=3, S=20, n_steps=2, device_synth=True)
 
 
 def test_against_committed_golden_vectors(cuda):
