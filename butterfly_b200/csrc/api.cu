@@ -237,6 +237,15 @@ int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int3
   });
 }
 
+int bfly_k_attn_prefill(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
+                        int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int B, int nq,
+                        void* out_bf16, void* stream) {
+  return guarded(nullptr, [&]() -> int {
+    KvLayout kv{const_cast<bf16*>(cb(kv_pages_bf16)), page_table, pages_per_seq, page_size, kv_local, head_dim};
+    return launch_attn_prefill(cb(q_bf16), kv, seq_lens, S, B, nq, mb(out_bf16), as_stream(stream));
+  });
+}
+
 int bfly_k_act(const float* in, int n_partials, int64_t partial_stride, const void* bias_bf16, int mode,
                int n_blocks, int f_block, const float* route_w, void* out_bf16, int T, void* stream) {
   return guarded(nullptr, [&]() -> int {

@@ -374,7 +374,10 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s));
     BFLY_TRY(launch_rope_kv(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, lens, S, T, q_local, kv_local, q, kv,
                             stream));
-    BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
+    if (S > 1)
+      BFLY_TRY(launch_attn_prefill(q, kv, lens, S, nb, q_local, attn_out, stream));
+    else
+      BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
     BFLY_TRY(gemm(w.wo, attn_out, q_local * dh, h, T, q_local * dh, &s));
     BFLY_TRY(row_parallel_finish(T, s, &pend_src, &pend_n));
     BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, w.bo, w.ffn_norm_w, w.ffn_norm_b, c.norm_eps,

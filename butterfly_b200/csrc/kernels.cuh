@@ -71,6 +71,10 @@ int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count);
 int launch_attn_decode(const bf16* q, KvLayout kv, const int* seq_lens, int S, int T, int nq, float* part_o,
                        float* part_ml, int n_splits, bf16* out, cudaStream_t stream);
 
+// attn_prefill.cu -- causal attention of S new tokens per sequence over the paged cache (tensor cores)
+int launch_attn_prefill(const bf16* q, KvLayout kv, const int* seq_lens, int S, int B, int nq, bf16* out,
+                        cudaStream_t stream);
+
 // gemm_tcgen05.cu -- C[n][m] (+= over split-K slices) = sum_k W[m][k] * X[n][k]; W, X bf16 K-major.
 struct GemmPlan {
   int M, N, K;          // M = weight rows (features), N = tokens

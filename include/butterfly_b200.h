@@ -121,6 +121,11 @@ int bfly_k_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, con
 int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
                        int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int T, int nq,
                        float* part_o, float* part_ml, int n_splits, void* out_bf16, void* stream);
+/* Causal attention of S new tokens per sequence (q is [B*S][nq*head_dim]); token s of sequence b sits at
+ * position seq_lens[b] + s and sees keys 0 .. seq_lens[b] + s, which must already be in the cache. */
+int bfly_k_attn_prefill(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
+                        int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int B, int nq,
+                        void* out_bf16, void* stream);
 /* Same computation as bfly_k_attn_decode for callers that cannot supply or allocate the split-context
  * scratch (the host application's pool owns all of the GPU's memory, cudaMalloc is banned from the
  * hot path, or a binding forwards only inputs and outputs).  The scratch is a fixed 4 MiB array inside

@@ -242,6 +242,26 @@ def test_attn_prefill_rows(lib, cuda):
         bf16_close(out[b * S:(b + 1) * S], want.reshape(S, nq * d), extra_abs=ATTN_ATOL)
 
 
+@pytest.mark.parametrize("d,nq,nk,S,lens0", [(128, 8, 2, 70, [0, 45]), (64, 12, 12, 33, [5, 0, 64]), (32, 8, 4, 100, [31]),
+                                              (128, 8, 1, 40, [0, 200]), (128, 4, 2, 129, [3])])
+def test_attn_prefill_tensor_core_kernel(lib, cuda, d, nq, nk, S, lens0):
+    """K7: causal attention of S new tokens over a (possibly non-empty) paged cache."""
+    ps, B = 32, len(lens0)
+    pps = (max(lens0) + S + ps - 1) // ps
+    kl, vl = gen((B * pps, nk, ps, d), 8, 1.0, torch.bfloat16), gen((B * pps, nk, ps, d), 10, 1.0, torch.bfloat16)
+    table = torch.randperm(B * pps, generator=torch.Generator().manual_seed(4)).to(torch.int32).reshape(B, pps)
+    q = gen((B * S, nq * d), 9, 1.0, torch.bfloat16)
+    out = torch.zeros((B * S, nq * d), dtype=torch.bfloat16, device=cuda)
+    ok(lib, lib.bfly_k_attn_prefill(D(q), D(pack_pages(kl, vl)), D(table), pps, ps, nk, d,
+                                    D(torch.tensor(lens0, dtype=torch.int32)), S, B, nq, out.data_ptr(), stream()))
+    for b in range(B):
+        pos = torch.arange(lens0[b] + S)
+        pg = table[b, pos // ps].long()
+        kk, vv = kl[pg, :, pos % ps, :].float(), vl[pg, :, pos % ps, :].float()
+        want = ops.attention(q[b * S:(b + 1) * S].float().reshape(1, S, nq, d), kk[None], vv[None], lens0[b])
+        bf16_close(out[b * S:(b + 1) * S], want.reshape(S, nq * d), extra_abs=ATTN_ATOL)
+
+
 @pytest.mark.parametrize("mode,n_blocks,fb,n_part,routed", [(0, 1, 512, 2, False), (1, 1, 3072, 1, False), (0, 4, 256, 3, True)])
 def test_act(lib, cuda, mode, n_blocks, fb, n_part, routed):
     T = 5
