@@ -197,6 +197,8 @@ def run_gpu(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.shard_of > 1:            # profiling aid: one rank's shard on one GPU, collectives skipped
+        os.environ["BFLY_SKIP_COLLECTIVES"] = "1"
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch N>1 with torchrun)"
     torch.cuda.set_device(local)
     dist = None
@@ -205,13 +207,14 @@ def run_gpu(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cfg = LLAMA3_8B if args.layers <= 0 else LLAMA3_8B.with_layers(args.layers)
-    tp = world
+    tp = world if args.shard_of <= 1 else args.shard_of
     plan = make_plan(cfg, tp)
     W, K = args.warmup, args.steps
     max_ctx = CTX + 2 * (max(W, 3) + K) + 16
     t_setup = time.perf_counter()
     model = Model(plan, rank, SyntheticSource(cfg, 0), device=local, max_batch=BATCH, max_ctx=max_ctx)
-    model.connect()
+    if args.shard_of <= 1:
+        model.connect()
     toks = synthetic_tokens(cfg, BATCH, CTX)
     lib, stream = model.lib, model.stream
 
@@ -293,7 +296,10 @@ def run_gpu(args):
             "prefill": {"tokens_per_s": BATCH * CTX / (prefill_ms / 1e3), "ms": prefill_ms, "tokens": BATCH * CTX},
             "setup_s": setup_s,
         }
-        if not args.no_cpu and world == 1:
+        if args.shard_of > 1:
+            line["INVALID"] = (f"profiling run: rank 0's shard of a tp={tp} plan on one GPU with the collectives "
+                               "skipped; per-rank compute time only, results are not a model output")
+        if not args.no_cpu and world == 1 and args.shard_of <= 1:
             v, sample, cores, _ = cpu_decode_sample()
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         print(json.dumps(line), flush=True)
@@ -311,6 +317,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layers", type=int, default=0, help="debug: reduce depth (the result is then NOT the headline config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--shard-of", type=int, default=0, help="profiling aid: run rank 0's shard of a tp=N plan on one "
+                    "GPU with the collectives skipped (the JSON line is marked INVALID)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

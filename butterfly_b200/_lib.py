@@ -63,6 +63,7 @@ SIGNATURES = {
     "bfly_k_lm_finalize": (i32, [vp, i32, i64, i32, i32, i32, vp, i64, vp, vp, vp]),
     "bfly_k_moe_router": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp]),
     "bfly_k_gemm": (i32, [vp, vp, i32, i32, i32, i64, i32, i32, i32, vp, i64, vp, i64, C.POINTER(i32), vp]),
+    "bfly_k_gemm_swiglu": (i32, [vp, vp, i32, i32, i32, i32, vp, i32, vp, vp]),
     "bfly_k_gemm_plan": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
 }
 
@@ -81,10 +82,15 @@ def load():
         if _lib is not None:
             return _lib
         path = _build.LIB
-        if not os.path.exists(path):
+        override = os.environ.get("BFLY_LIB")     # A/B profiling of another build of the same ABI
+        if override:
+            path = override
+        elif not os.path.exists(path):
             path = _build.build_library()
         lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
         for name, (res, args) in SIGNATURES.items():
+            if override and not hasattr(lib, name):
+                continue
             fn = getattr(lib, name)          # AttributeError if the symbol is not exported
             fn.restype, fn.argtypes = res, args
         _lib = lib

@@ -296,19 +296,44 @@ int bfly_k_gemm_plan(int M, int N, int K, int* splits, int* bn, int* stages) {
 }
 
 int bfly_k_gemm(const void* w_bf16, const void* x_bf16, int M, int N, int K, int64_t ldx, int splits, int bn,
-                int stages, float* out_f32, int64_t split_stride, void* out_bf16, int64_t ldc, int* splits_used,
+                int stages, float* out_f32, int64_t split_stride, void* out_bf16, int64_t ldc, int* slices_written,
                 void* stream) {
   return guarded(nullptr, [&]() -> int {
     BFLY_CHECK(w_bf16 && x_bf16 && M > 0 && N > 0 && K > 0, "gemm: null operand or empty shape");
     int dev = 0, sms = 148;
     BFLY_CUDA(cudaGetDevice(&dev));
     BFLY_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    GemmPlan p = gemm_plan(M, N, K, sms, out_bf16 ? 1 : kMaxSplits);
-    if (splits > 0) p.splits = splits;
+    GemmPlan p = gemm_plan(M, N, K, sms, kMaxSplits);
     if (bn > 0) p.bn = bn;
+    if (splits > 0) {
+      p.splits = splits;
+      p.cluster = (splits > 1 && splits <= 8 && p.bn <= 64) ? 1 : 0;
+    }
     if (stages > 0) p.stages = stages;
-    if (splits_used) *splits_used = p.splits;
+    if (slices_written) *slices_written = gemm_slices(p);
     return launch_gemm(cb(w_bf16), cb(x_bf16), ldx, p, out_f32, split_stride, mb(out_bf16), ldc, as_stream(stream));
+  });
+}
+
+int bfly_k_gemm_swiglu(const void* w_gate_up_bf16, const void* x_bf16, int N, int K, int n_blocks, int f_block,
+                       const float* route_w, int splits, void* act_out_bf16, void* stream) {
+  return guarded(nullptr, [&]() -> int {
+    BFLY_CHECK(w_gate_up_bf16 && x_bf16 && act_out_bf16 && N > 0 && K > 0 && n_blocks > 0 && f_block > 0,
+               "gemm_swiglu: null operand or empty shape");
+    int dev = 0, sms = 148;
+    BFLY_CUDA(cudaGetDevice(&dev));
+    BFLY_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    GemmPlan p = gemm_plan(n_blocks * f_block, N, K, sms, kMaxSplits, 1);
+    if (splits > 0) {
+      BFLY_CHECK(splits == 1 || (splits <= 8 && p.bn <= 64), "gemm_swiglu: splits > 1 needs a cluster (<= 8, N <= 64)");
+      p.splits = splits;
+      p.cluster = splits > 1 ? 1 : 0;
+    }
+    GemmOut o{};
+    o.out_bf16 = mb(act_out_bf16);
+    o.ldc = (int64_t)n_blocks * f_block;
+    o.n_blocks = n_blocks; o.f_block = f_block; o.route_w = route_w;
+    return launch_gemm_ex(cb(w_gate_up_bf16), cb(x_bf16), K, p, o, as_stream(stream));
   });
 }
 

@@ -192,11 +192,91 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_partials, in
   }
 }
 
+// Prefill variant: a CTA owns 32 consecutive tokens of one sequence and one head, stages the rotated
+// values in shared memory and writes q rows, K rows and the TRANSPOSED V block with consecutive threads
+// on consecutive addresses (the per-token kernel above would scatter 2-byte V stores 64 bytes apart).
+constexpr int kRopeTile = 32;
+__global__ void __launch_bounds__(256) rope_kv_tile_kernel(
+    const float* __restrict__ qkv, int n_partials, int64_t partial_stride, const bf16* __restrict__ bias,
+    const float2* __restrict__ rope_table, const int* __restrict__ seq_lens, int S, int nq, int nk,
+    bf16* __restrict__ q_out, KvLayout kv) {
+  extern __shared__ float tile[];                     // [32][d + 1]
+  pdl_trigger();
+  pdl_wait();
+  const int s0 = blockIdx.x * kRopeTile, head = blockIdx.y, b = blockIdx.z;
+  const int d = kv.head_dim, half = d >> 1, ldt = d + 1;
+  const int ld = (nq + 2 * nk) * d;
+  const int n_tok = min(kRopeTile, S - s0);
+  const int pos0 = seq_lens[b] + s0;
+  const bool rotate = rope_table != nullptr && head < nq + nk;
+  for (int idx = threadIdx.x; idx < n_tok * half; idx += blockDim.x) {
+    const int tok = idx / half, i = idx - tok * half;
+    const int c0 = head * d + i, c1 = c0 + half;
+    const float* src = qkv + (int64_t)(b * S + s0 + tok) * ld;
+    float x0 = 0.f, x1 = 0.f;
+    for (int p = 0; p < n_partials; ++p) {
+      x0 += src[p * partial_stride + c0];
+      x1 += src[p * partial_stride + c1];
+    }
+    if (bias != nullptr) {
+      x0 += __bfloat162float(bias[c0]);
+      x1 += __bfloat162float(bias[c1]);
+    }
+    if (rotate) {
+      const float2 cs = rope_table[(int64_t)(pos0 + tok) * half + i];
+      const float y0 = x0 * cs.x - x1 * cs.y, y1 = x1 * cs.x + x0 * cs.y;
+      x0 = y0; x1 = y1;
+    }
+    tile[tok * ldt + i] = x0;
+    tile[tok * ldt + i + half] = x1;
+  }
+  __syncthreads();
+  if (head < nq) {
+    for (int idx = threadIdx.x; idx < n_tok * half; idx += blockDim.x) {
+      const int tok = idx / half, dd = (idx - tok * half) * 2;
+      bf16* dst = q_out + ((int64_t)(b * S + s0 + tok) * nq + head) * d + dd;
+      *reinterpret_cast<uint32_t*>(dst) = pack_bf16(tile[tok * ldt + dd], tile[tok * ldt + dd + 1]);
+    }
+    return;
+  }
+  const int which = (head < nq + nk) ? 0 : 1;
+  const int kh = (head - nq) - which * nk;
+  const int ps = kv.page_size;
+  if (which == 0) {
+    for (int idx = threadIdx.x; idx < n_tok * half; idx += blockDim.x) {
+      const int tok = idx / half, dd = (idx - tok * half) * 2;
+      const int pos = pos0 + tok;
+      const int page = kv.page_table[(int64_t)b * kv.pages_per_seq + pos / ps];
+      bf16* blk = kv.base + (((int64_t)page * 2) * kv.kv_local + kh) * ps * d;
+      *reinterpret_cast<uint32_t*>(blk + kv_k_offset(pos % ps, dd, d)) =
+          pack_bf16(tile[tok * ldt + dd], tile[tok * ldt + dd + 1]);
+    }
+  } else {
+    for (int idx = threadIdx.x; idx < d * kRopeTile; idx += blockDim.x) {
+      const int dd = idx / kRopeTile, tok = idx - dd * kRopeTile;
+      if (tok >= n_tok) continue;
+      const int pos = pos0 + tok;
+      const int page = kv.page_table[(int64_t)b * kv.pages_per_seq + pos / ps];
+      bf16* blk = kv.base + (((int64_t)page * 2 + 1) * kv.kv_local + kh) * ps * d;
+      blk[kv_v_offset(pos % ps, dd, d)] = __float2bfloat16_rn(tile[tok * ldt + dd]);
+    }
+  }
+}
+
 int launch_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, const bf16* bias,
                    const float2* rope_table, const int* seq_lens, int S, int T, int nq, int nk, bf16* q_out,
                    KvLayout kv, cudaStream_t stream) {
   BFLY_CHECK(T > 0 && n_partials >= 1 && kv.head_dim % 2 == 0 && kv.head_dim <= 2048, "rope_kv: bad shape");
   BFLY_CHECK(nk == kv.kv_local, "rope_kv: nk must equal the cache's kv heads");
+  if (S >= kRopeTile && T % S == 0) {
+    dim3 tgrid(ceil_div(S, kRopeTile), nq + 2 * nk, T / S);
+    BFLY_CHECK(T / S <= 65535, "rope_kv: too many sequences in one call");
+    const size_t smem = (size_t)kRopeTile * (kv.head_dim + 1) * sizeof(float);
+    BFLY_CUDA(launch_pdl(rope_kv_tile_kernel, tgrid, dim3(256), smem, stream, qkv, n_partials, partial_stride, bias,
+                         rope_table, seq_lens, S, nq, nk, q_out, kv));
+    count_launch();
+    return BFLY_OK;
+  }
   dim3 grid(T, nq + 2 * nk);
   BFLY_CUDA(launch_pdl(rope_kv_kernel, dim3(grid), dim3(kv.head_dim / 2), 0, stream, qkv, n_partials, partial_stride, bias, rope_table, seq_lens,
                                                       S, nq, nk, q_out, kv));

@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -124,6 +125,10 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   e->n_pages = (int64_t)c.max_batch * e->pages_per_seq;
   e->layer_kv_elems = e->n_pages * 2 * e->kv_local * c.page_size * c.head_dim;
   e->layers.resize(c.n_layers);
+  {
+    const char* env = getenv("BFLY_FUSED_SWIGLU");      // tuning knob; default on
+    e->fused_swiglu = !(env && env[0] == '0');
+  }
 
   const int h = c.hidden, maxT = c.max_tokens, maxB = c.max_batch;
   // split-K scratch: worst case over every GEMM shape and every token count a forward can see
@@ -321,34 +326,60 @@ int Engine::comm_init(const void* id128, int world, int rank) {
   return BFLY_OK;
 }
 
+// Profiling aid: BFLY_SKIP_COLLECTIVES=1 lets ONE process run rank r's shard of a tp > 1 plan with the
+// collectives left out (results are then wrong by construction; bench.py --shard-of labels them so).
+static bool skip_collectives() {
+  static const bool v = [] { const char* e = getenv("BFLY_SKIP_COLLECTIVES"); return e && e[0] == '1'; }();
+  return v;
+}
+
 int Engine::all_reduce_f32(float* buf, size_t count) {
   if (d.tp == 1) return BFLY_OK;
+  if (!comm && skip_collectives()) return BFLY_OK;
   if (!comm) { set_error("tp > 1 but bfly_comm_init was not called"); return BFLY_ESTATE; }
   BFLY_NCCL(g_nccl.AllReduce(buf, buf, count, kNcclFloat, kNcclSum, comm, stream));
   return BFLY_OK;
 }
 
 int Engine::all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank) {
+  if (!comm && skip_collectives()) return BFLY_OK;
   if (!comm) { set_error("tp > 1 but bfly_comm_init was not called"); return BFLY_ESTATE; }
   BFLY_NCCL(g_nccl.AllGather(src, dst, bytes_per_rank, kNcclInt8, comm, stream));
   return BFLY_OK;
 }
 
 // ---- forward -----------------------------------------------------------------------------------
-int Engine::gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* splits_out) {
+int Engine::gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out) {
   const GemmPlan p = gemm_plan(M, N, K, sm_count, kMaxSplits);
-  if ((size_t)p.splits * N * M > ws_elems) { set_error("split-K scratch too small (internal sizing error)"); return BFLY_ESTATE; }
-  *splits_out = p.splits;
+  const int slices = gemm_slices(p);
+  if ((size_t)slices * N * M > ws_elems) { set_error("split-K scratch too small (internal sizing error)"); return BFLY_ESTATE; }
+  *slices_out = slices;
   return launch_gemm(W, X, ldx, p, ws, (int64_t)N * M, nullptr, M, stream);
 }
 
+// gate/up projection with the SwiGLU (and the MoE routing weight) fused into the GEMM epilogue
+int Engine::gemm_swiglu(const bf16* W, const bf16* X, int N) {
+  const GemmPlan p = gemm_plan(ffn_act_cols, N, d.hidden, sm_count, kMaxSplits, 1);
+  GemmOut o{};
+  o.out_bf16 = act;
+  o.ldc = ffn_act_cols;
+  o.n_blocks = n_blocks;
+  o.f_block = f_block;
+  o.route_w = d.n_experts ? route_w : nullptr;
+  return launch_gemm_ex(W, X, d.hidden, p, o, stream);
+}
+
 // Row-parallel output: fold slices and all-reduce when tp > 1; tells the consumer where to read.
-int Engine::row_parallel_finish(int T, int splits, const float** src, int* n_partials) {
+int Engine::row_parallel_finish(int T, int slices, const float** src, int* n_partials) {
   const int h = d.hidden;
-  if (d.tp == 1) { *src = ws; *n_partials = splits; return BFLY_OK; }
-  BFLY_TRY(launch_reduce_partials(ws, splits, (int64_t)T * h, red, (int64_t)T * h, stream));
-  BFLY_TRY(all_reduce_f32(red, (size_t)T * h));
-  *src = red; *n_partials = 1;
+  if (d.tp == 1) { *src = ws; *n_partials = slices; return BFLY_OK; }
+  float* buf = ws;
+  if (slices > 1) {
+    BFLY_TRY(launch_reduce_partials(ws, slices, (int64_t)T * h, red, (int64_t)T * h, stream));
+    buf = red;
+  }
+  BFLY_TRY(all_reduce_f32(buf, (size_t)T * h));
+  *src = buf; *n_partials = 1;
   return BFLY_OK;
 }
 
@@ -385,9 +416,15 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     if (c.n_experts)
       BFLY_TRY(launch_moe_router(xn, w.router, T, h, c.n_experts, c.top_k, c.rank * experts_local, experts_local,
                                  route_w, stream));
-    BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s));
-    BFLY_TRY(launch_act(ws, s, (int64_t)T * ffn_in_rows, w.b_up, gated ? ACT_SWIGLU : ACT_GELU_TANH, n_blocks, f_block,
-                        c.n_experts ? route_w : nullptr, act, T, stream));
+    // Fused SwiGLU epilogue: +5 % at prefill (no fp32 gate/up round trip); at decode the cluster it needs
+    // to complete the K sum costs more than the separate activation kernel (measured), so T <= 64 stays unfused.
+    if (gated && fused_swiglu && T > 64) {
+      BFLY_TRY(gemm_swiglu(w.w_in, xn, T));
+    } else {
+      BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s));
+      BFLY_TRY(launch_act(ws, s, (int64_t)T * ffn_in_rows, w.b_up, gated ? ACT_SWIGLU : ACT_GELU_TANH, n_blocks,
+                          f_block, c.n_experts ? route_w : nullptr, act, T, stream));
+    }
     BFLY_TRY(gemm(w.w_down, act, ffn_act_cols, h, T, ffn_act_cols, &s));
     BFLY_TRY(row_parallel_finish(T, s, &pend_src, &pend_n));
     pend_bias = w.b_down;

@@ -44,6 +44,7 @@ struct Engine {
   int q_local = 0, kv_local = 0, qkv_rows = 0, experts_local = 0;
   int n_blocks = 1, f_block = 0, ffn_in_rows = 0, ffn_act_cols = 0;
   bool gated = true;
+  bool fused_swiglu = true;                // gate/up GEMM applies the SwiGLU in its epilogue
   int v_shard = 0, v0 = 0, v_local = 0;
   int pages_per_seq = 0;
   int64_t n_pages = 0, layer_kv_elems = 0;
@@ -93,7 +94,8 @@ struct Engine {
  private:
   int find(const std::string& name, int64_t rows, int64_t cols, bool required, bf16** out);
   int check_ready(int B);
-  int gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* splits_out);
+  int gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out);
+  int gemm_swiglu(const bf16* W, const bf16* X, int N);
   int row_parallel_finish(int T, int splits, const float** src, int* n_partials);
   int all_reduce_f32(float* buf, size_t count);
   int all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank);

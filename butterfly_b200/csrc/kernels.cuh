@@ -77,16 +77,30 @@ int launch_attn_prefill(const bf16* q, KvLayout kv, const int* seq_lens, int S, 
 
 // gemm_tcgen05.cu -- C[n][m] (+= over split-K slices) = sum_k W[m][k] * X[n][k]; W, X bf16 K-major.
 struct GemmPlan {
-  int M, N, K;          // M = weight rows (features), N = tokens
+  int M, N, K;          // M = output features (dual: gated features = half the weight rows), N = tokens
   int bn;               // token tile (UMMA N), multiple of 16, <= 256
-  int splits;           // split-K factor; each slice is written to out + s * split_stride
+  int splits;           // split-K factor
+  int cluster;          // 1: the K-slices form a thread-block cluster and are reduced through DSMEM into ONE
+                        //    output (deterministic, rank order); 0: each slice is written to out + s * split_stride
+  int dual;             // 1: W = n_blocks x [gate(f_block) | up(f_block)] rows, fused SwiGLU epilogue (bf16 out)
   int stages;
   size_t smem_bytes;
 };
+struct GemmOut {
+  float* out_f32;       // fp32 [slices][N][ldc]   (slices = 1 when the plan reduces in-cluster or splits == 1)
+  int64_t split_stride;
+  bf16* out_bf16;       // bf16 [N][ldc]           (needs one complete K sum)
+  int64_t ldc;
+  int n_blocks, f_block;    // dual only
+  const float* route_w;     // dual + MoE: [N][n_blocks], nullptr otherwise
+};
 int gemm_init();        // resolves cuTensorMapEncodeTiled, sets kernel attributes (once per process)
-GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits);
-// out_bf16 != nullptr requires splits == 1 (direct bf16 output); otherwise fp32 slices in out_f32.
+GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual = 0);
+// number of fp32 slices a consumer must fold for this plan
+inline int gemm_slices(const GemmPlan& p) { return (p.cluster || p.splits == 1) ? 1 : p.splits; }
 // ldx = row pitch of X in elements (>= K, multiple of 8).
+int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& plan, const GemmOut& out,
+                   cudaStream_t stream);
 int launch_gemm(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& plan, float* out_f32,
                 int64_t split_stride, bf16* out_bf16, int64_t ldc, cudaStream_t stream);
 

@@ -144,12 +144,17 @@ int bfly_k_lm_finalize(const float* partials, int n_partials, int64_t partial_st
                        float* logits, int64_t logits_ld, uint64_t* keys, int32_t* tokens_out, void* stream);
 int bfly_k_moe_router(const void* xn_bf16, const void* router_bf16, int T, int h, int n_experts, int top_k,
                       int first_local, int n_local, float* route_w, void* stream);
-/* C[n][m] = sum_k W[m][k] X[n][k].  splits/bn/stages <= 0 pick the planner's choice; the chosen
- * split count is returned through *splits_used.  out_f32 receives `splits` slices `split_stride`
- * floats apart (row pitch ldc); out_bf16 (splits must resolve to 1) receives bf16 directly. */
+/* C[n][m] = sum_k W[m][k] X[n][k].  splits/bn/stages <= 0 pick the planner's choice.  K-slices of token
+ * tiles <= 64 wide and splits <= 8 are reduced inside a thread-block cluster (one output slice);
+ * otherwise out_f32 receives one fp32 slice per split, `split_stride` floats apart (row pitch ldc).
+ * *slices_written tells the caller how many slices to fold.  out_bf16 needs a single complete sum. */
 int bfly_k_gemm(const void* w_bf16, const void* x_bf16, int M, int N, int K, int64_t ldx, int splits, int bn,
-                int stages, float* out_f32, int64_t split_stride, void* out_bf16, int64_t ldc, int* splits_used,
+                int stages, float* out_f32, int64_t split_stride, void* out_bf16, int64_t ldc, int* slices_written,
                 void* stream);
+/* act[n][b*f_block + j] = route_w[n][b] * silu(x . gate_row) * (x . up_row) for W = n_blocks blocks of
+ * [gate(f_block) | up(f_block)] rows: the gate/up projection with the SwiGLU fused into the epilogue. */
+int bfly_k_gemm_swiglu(const void* w_gate_up_bf16, const void* x_bf16, int N, int K, int n_blocks, int f_block,
+                       const float* route_w, int splits, void* act_out_bf16, void* stream);
 int bfly_k_gemm_plan(int M, int N, int K, int* splits, int* bn, int* stages);
 
 #ifdef __cplusplus

@@ -140,6 +140,43 @@ def test_gemm_split_slices(lib, cuda, M, N, K):
         assert err < 2e-3 * max(1.0, want.abs().max().item()), f"splits={used.value} max err {err}"
 
 
+@pytest.mark.parametrize("N,K,n_blocks,fb,splits,routed", [
+    (32, 1024, 1, 512, 1, False), (32, 4096, 1, 1792, 4, False), (32, 2048, 1, 256, 8, False), (7, 512, 3, 200, 2, True),
+    (300, 1024, 1, 384, 1, False), (64, 768, 2, 128, 3, True), (20, 4096, 1, 3584, 0, False)])
+def test_gemm_fused_swiglu(lib, cuda, N, K, n_blocks, fb, splits, routed):
+    """gate/up projection with the SwiGLU (and MoE routing weight) in the epilogue; splits > 1 reduces the
+    K-slices inside a thread-block cluster through distributed shared memory."""
+    W = gen((n_blocks * 2 * fb, K), 1, 0.03, torch.bfloat16).to(cuda)
+    X = gen((N, K), 2, 1.0, torch.bfloat16).to(cuda)
+    rw = torch.rand((N, n_blocks), generator=torch.Generator().manual_seed(3))
+    rw[rw < 0.3] = 0.0
+    rw_d = rw.to(cuda)
+    out = torch.full((N, n_blocks * fb), float("nan"), dtype=torch.bfloat16, device=cuda)
+    ok(lib, lib.bfly_k_gemm_swiglu(W.data_ptr(), X.data_ptr(), N, K, n_blocks, fb, rw_d.data_ptr() if routed else None,
+                                   splits, out.data_ptr(), stream()))
+    gu = (X.float() @ W.float().t()).cpu().reshape(N, n_blocks, 2 * fb)
+    want = ops.swiglu(gu)
+    if routed:
+        want = want * rw[:, :, None]
+    assert not torch.isnan(out.float()).any()
+    bf16_close(out, want.reshape(N, n_blocks * fb), extra_abs=2e-3)
+
+
+def test_gemm_cluster_reduce_is_deterministic(lib, cuda):
+    M, N, K = 4096, 32, 4096
+    W, X = gen((M, K), 1, 0.05, torch.bfloat16).to(cuda), gen((N, K), 2, 1.0, torch.bfloat16).to(cuda)
+    outs = []
+    for _ in range(3):
+        out = torch.zeros((N, M), dtype=torch.float32, device=cuda)
+        used = C.c_int32(0)
+        ok(lib, lib.bfly_k_gemm(W.data_ptr(), X.data_ptr(), M, N, K, K, 8, 0, 0, out.data_ptr(), N * M, None, M,
+                                C.byref(used), stream()))
+        assert used.value == 1
+        outs.append(out.cpu())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    assert (outs[0] - (X.float() @ W.float().t()).cpu()).abs().max().item() < 5e-3
+
+
 def test_gemm_bf16_out_and_pitched_x(lib, cuda):
     M, N, K, S = 512, 6, 1024, 5
     W = gen((M, K), 1, 0.05, torch.bfloat16).to(cuda)
@@ -154,9 +191,10 @@ def test_gemm_bf16_out_and_pitched_x(lib, cuda):
     bf16_close(out, want, extra_abs=2e-3)
 
 
+@pytest.mark.parametrize("S", [4, 45])          # S >= 32 takes the tiled prefill kernel
 @pytest.mark.parametrize("d,nq,nk,theta,use_bias", [(128, 4, 1, 5e5, False), (64, 6, 6, 0.0, True), (32, 4, 2, 1e6, False)])
-def test_rope_kv(lib, cuda, d, nq, nk, theta, use_bias):
-    B, S, ps, pps, n_part = 3, 4, 32, 2, 2
+def test_rope_kv(lib, cuda, d, nq, nk, theta, use_bias, S):
+    B, ps, pps, n_part = 3, 32, 3, 2
     T, ld = B * S, (nq + 2 * nk) * d
     lens = torch.tensor([0, 9, 21], dtype=torch.int32)
     qkv = gen((n_part, T, ld), 1, 0.7)
@@ -164,7 +202,7 @@ def test_rope_kv(lib, cuda, d, nq, nk, theta, use_bias):
     perm = torch.randperm(B * pps, generator=torch.Generator().manual_seed(5)).to(torch.int32).reshape(B, pps)
     pages = torch.zeros((B * pps, 2, nk, ps * d), dtype=torch.bfloat16, device=cuda)
     half = d // 2
-    max_pos = 64
+    max_pos = 96
     inv = theta ** (-torch.arange(0, half, dtype=torch.float64) * 2.0 / d) if theta > 0 else None
     table = None
     if theta > 0:

@@ -79,6 +79,25 @@ def tune_gemm(tp=1, batch=32):
         del Ws
 
 
+def tune_swiglu(tp=1, batch=32):
+    """gate/up projection with the fused SwiGLU epilogue: cluster split sweep."""
+    lib = _lib.load()
+    h, f = 4096, 14336 // tp
+    n_buf = 3 if tp == 1 else 8
+    Ws = [torch.randn((2 * f, h), device="cuda").mul_(0.02).to(torch.bfloat16) for _ in range(n_buf)]
+    X = torch.randn((batch, h), device="cuda").to(torch.bfloat16)
+    out = torch.empty((batch, f), device="cuda", dtype=torch.bfloat16)
+    pk = peak()
+    print(f"== fused gate/up+SwiGLU: f={f} N={batch} K={h} ({2 * f * h * 2 / 1e6:.1f} MB)")
+    for splits in (0, 1, 2, 3, 4, 5, 6, 8):
+        def fn(i):
+            rc = lib.bfly_k_gemm_swiglu(Ws[i % n_buf].data_ptr(), X.data_ptr(), batch, h, 1, f, None, splits,
+                                        out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+            assert rc == 0, lib.bfly_last_error(None)
+        ms = time_launches(fn, 4 * n_buf)
+        print(f"  splits={splits} (0=planner): {ms * 1e3:6.1f} us  {2 * f * h * 2 / ms / 1e6 / pk * 100:4.0f}%")
+
+
 def tune_attn(tp=1, batch=32, ctx=2048):
     lib = _lib.load()
     nq, nk, d, ps = 32 // tp, 8 // tp, 128, 32
@@ -114,6 +133,8 @@ if __name__ == "__main__":
         tune_gemm(tp)
     elif what == "attn":
         tune_attn(tp)
+    elif what == "swiglu":
+        tune_swiglu(tp)
     else:
         tune_gemm(tp)
         tune_attn(tp)
