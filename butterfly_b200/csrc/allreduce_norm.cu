@@ -1,0 +1,144 @@
+// C1 fused into K3 for decode: the partial-sum all-reduce after a row-parallel GEMM, the residual
+// add and the following norm in ONE kernel over NVLink peer memory (SURVEY.md rows a10 + a4).
+//
+// Every rank runs this kernel with one CTA per token row.  The CTA folds its rank's split-K slices of
+// the row, PUSHES the fp32 row into a slot of every rank's receive buffer (peer-mapped stores through
+// NVSwitch), publishes an epoch flag next to it with release semantics at system scope, waits until
+// the same row has arrived from every rank, and then sums the tp contributions from its OWN memory in
+// rank order -- so every rank computes a bit-identical residual -- adds the bias, normalises and writes
+// the next GEMM's bf16 operand.  Synchronisation is per row (no grid barrier); buffers are double
+// buffered by call parity and flags carry a monotonically increasing epoch, so nothing is ever reset.
+// A rank can be at most one call ahead of a peer (its next call needs that peer's flag), which is what
+// makes two parities sufficient.  Latency regime only (T <= max_batch rows); prefill keeps NCCL.
+#include <algorithm>
+
+#include "kernels.cuh"
+
+namespace bfly {
+
+namespace {
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// the receive buffer is written by other GPUs: read it around L1
+__device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+
+__global__ void __launch_bounds__(1024) ar_add_norm_kernel(
+    float* __restrict__ residual, const float* __restrict__ partials, int n_partials, int64_t partial_stride,
+    const bf16* __restrict__ bias, const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float eps,
+    int layer_norm, bf16* __restrict__ out, int h, ArPeers peers, int call_idx, const unsigned* __restrict__ step_ptr,
+    int calls_per_step) {
+  extern __shared__ __align__(16) float srow[];
+  __shared__ float red[32];
+  pdl_trigger();
+  pdl_wait();
+  const int row = blockIdx.x, tp = peers.tp, me = peers.rank;
+  const unsigned epoch = (*step_ptr) * (unsigned)calls_per_step + (unsigned)call_idx + 1u;
+  const int parity = call_idx & 1;
+  const int64_t slot_me = ((int64_t)(parity * tp + me) * peers.max_rows + row);
+
+  // 1) fold this rank's slices of the row and push it to every rank (including this one)
+  for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
+    const float* pp = partials + (int64_t)row * h + i;
+    float4 v = *reinterpret_cast<const float4*>(pp);
+    for (int p = 1; p < n_partials; ++p) {
+      const float4 a = *reinterpret_cast<const float4*>(pp + p * partial_stride);
+      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+    }
+    for (int r = 0; r < tp; ++r) *reinterpret_cast<float4*>(peers.recv[r] + slot_me * h + i) = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  // 2) publish the epoch flag at every rank, 3) wait for every rank's row
+  if ((int)threadIdx.x < tp) st_release_sys_u32(peers.flags[threadIdx.x] + slot_me, epoch);
+  if ((int)threadIdx.x < tp) {
+    const unsigned* f = peers.flags[me] + ((int64_t)(parity * tp + (int)threadIdx.x) * peers.max_rows + row);
+    const long long t0 = clock64();
+    while (ld_acquire_sys_u32(f) != epoch) {
+      if (clock64() - t0 > 8000000000ll) __trap();     // a lost peer must not hang the GPU
+    }
+  }
+  __syncthreads();
+
+  // 4) sum in rank order from local memory, residual add, norm
+  float* res = residual + (int64_t)row * h;
+  float sum = 0.f, sumsq = 0.f;
+  for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
+    float4 v = *reinterpret_cast<const float4*>(res + i);
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < tp; ++r) {
+      const float4 x = ld_volatile_f4(peers.recv[me] + ((int64_t)(parity * tp + r) * peers.max_rows + row) * h + i);
+      a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+    }
+    v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+    if (bias != nullptr) {
+      const uint2 b = *reinterpret_cast<const uint2*>(bias + i);
+      v.x += bf16_lo(b.x); v.y += bf16_hi(b.x); v.z += bf16_lo(b.y); v.w += bf16_hi(b.y);
+    }
+    *reinterpret_cast<float4*>(res + i) = v;
+    *reinterpret_cast<float4*>(srow + i) = v;
+    sum += (v.x + v.y) + (v.z + v.w);
+    sumsq += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+  }
+  float mean = 0.f, rstd;
+  if (layer_norm) {
+    mean = block_sum(sum, red) / (float)h;
+    float var = 0.f;
+    for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
+      const float4 v = *reinterpret_cast<const float4*>(srow + i);
+      const float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
+      var += (a * a + b * b) + (c * c + d * d);
+    }
+    var = block_sum(var, red) / (float)h;
+    rstd = 1.0f / sqrtf(var + eps);
+  } else {
+    rstd = 1.0f / sqrtf(block_sum(sumsq, red) / (float)h + eps);
+  }
+  bf16* o = out + (int64_t)row * h;
+  for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(srow + i);
+    const uint2 g = *reinterpret_cast<const uint2*>(gamma + i);
+    float y0 = (v.x - mean) * rstd * bf16_lo(g.x), y1 = (v.y - mean) * rstd * bf16_hi(g.x);
+    float y2 = (v.z - mean) * rstd * bf16_lo(g.y), y3 = (v.w - mean) * rstd * bf16_hi(g.y);
+    if (beta != nullptr) {
+      const uint2 b = *reinterpret_cast<const uint2*>(beta + i);
+      y0 += bf16_lo(b.x); y1 += bf16_hi(b.x); y2 += bf16_lo(b.y); y3 += bf16_hi(b.y);
+    }
+    *reinterpret_cast<uint2*>(o + i) = make_uint2(pack_bf16(y0, y1), pack_bf16(y2, y3));
+  }
+}
+
+}  // namespace
+
+int launch_ar_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
+                       const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
+                       int T, int h, const ArPeers& peers, int call_idx, const unsigned* step_ptr, int calls_per_step,
+                       cudaStream_t stream) {
+  BFLY_CHECK(T > 0 && T <= peers.max_rows && h % 4 == 0 && h * 4 <= 160 * 1024, "ar_add_norm: bad shape");
+  BFLY_CHECK(n_partials >= 1 && partials != nullptr && peers.tp >= 2 && peers.tp <= kMaxPeers, "ar_add_norm: bad peers");
+  const size_t smem = (size_t)h * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    BFLY_CUDA(cudaFuncSetAttribute(ar_add_norm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    attr_set = true;
+  }
+  const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
+  BFLY_CUDA(launch_pdl(ar_add_norm_kernel, dim3(T), dim3(threads), smem, stream, residual, partials, n_partials,
+                       partial_stride, bias, gamma, beta, eps, layer_norm, out, h, peers, call_idx, step_ptr,
+                       calls_per_step));
+  count_launch();
+  return BFLY_OK;
+}
+
+}  // namespace bfly

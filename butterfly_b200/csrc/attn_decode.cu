@@ -276,13 +276,14 @@ int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, i
 // Choose the context split so that (token x kv-head x split) CTAs fill whole waves of SMs (one CTA per
 // SM: the rings take ~200 KB of shared memory) while every CTA keeps at least a few tiles per warp.
 int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count) {
+  (void)sm_count;
   const int base = std::max(1, T * kv_local);
   const int tiles = std::max(1, (max_ctx + kTile - 1) / kTile);
-  // Measured on B200 (tools/tune_kernels.py attn): splitting only pays while there are fewer CTAs than
-  // SMs -- each extra split adds a ring ramp-up and a slice for the combine kernel.  Take the smallest
-  // split that gives every SM a CTA, keeping at least two tiles per warp.
+  // Measured on B200 (tools/tune_kernels.py attn, B=32 ctx=2048): 256 or 128 (sequence, kv head) CTAs run
+  // fastest unsplit (79-81 % of HBM peak), 64 want 2 splits, 32 want 3 -- every split adds a ring
+  // ramp-up and a slice for the combine kernel, so split only until ~96 CTAs exist.
   int n = 1;
-  while (base * n < sm_count && n < 32 && tiles / (n + 1) >= 2 * kWarps) ++n;
+  while (base * n < 96 && n < 32 && tiles / (n + 1) >= 2 * kWarps) ++n;
   return n;
 }
 

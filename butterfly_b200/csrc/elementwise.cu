@@ -423,16 +423,17 @@ int launch_pick_tokens_pitched(const unsigned long long* keys, int n_ranks, int 
   return BFLY_OK;
 }
 
-__global__ void advance_kernel(int* seq_lens, int B, int S, int* step_counter) {
+__global__ void advance_kernel(int* seq_lens, int B, int S, int* step_counter, unsigned* ar_step) {
   pdl_trigger();
   pdl_wait();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < B) seq_lens[b] += S;
   if (b == 0 && step_counter != nullptr) *step_counter += 1;
+  if (b == 0 && ar_step != nullptr) *ar_step += 1u;
 }
 
-int launch_advance(int* seq_lens, int B, int S, int* step_counter, cudaStream_t stream) {
-  BFLY_CUDA(launch_pdl(advance_kernel, dim3(ceil_div(B, 128)), dim3(128), 0, stream, seq_lens, B, S, step_counter));
+int launch_advance(int* seq_lens, int B, int S, int* step_counter, unsigned* ar_step, cudaStream_t stream) {
+  BFLY_CUDA(launch_pdl(advance_kernel, dim3(ceil_div(B, 128)), dim3(128), 0, stream, seq_lens, B, S, step_counter, ar_step));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;

@@ -214,6 +214,7 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
 Engine::~Engine() {
   for (auto& kv : graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  for (void* p : ipc_opened) cudaIpcCloseMemHandle(p);
   if (comm && g_nccl.CommDestroy) g_nccl.CommDestroy(comm);
   for (void* p : allocations) cudaFree(p);
   if (pinned) cudaFreeHost(pinned);
@@ -323,6 +324,49 @@ int Engine::comm_init(const void* id128, int world, int rank) {
   NcclId id;
   std::memcpy(id.bytes, id128, 128);
   BFLY_NCCL(g_nccl.CommInitRank(&comm, world, id, rank));
+  const char* env = getenv("BFLY_P2P_ALLREDUCE");            // tuning knob; default on
+  if (!(env && env[0] == '0')) BFLY_TRY(p2p_init());
+  return BFLY_OK;
+}
+
+// Peer-mapped receive buffers for the fused decode all-reduce: every rank allocates one buffer,
+// the CUDA IPC handles travel through an NCCL all-gather, and each rank maps its peers' buffers.
+int Engine::p2p_init() {
+  const int tp = d.tp, max_rows = d.max_batch, h = d.hidden;
+  const size_t flags_bytes = (((size_t)2 * tp * max_rows * sizeof(unsigned)) + 255) / 256 * 256;
+  const size_t recv_bytes = (size_t)2 * tp * max_rows * h * sizeof(float);
+  char* base = nullptr;
+  BFLY_TRY(dev_alloc(this, &base, flags_bytes + recv_bytes, &workspace_bytes));
+  BFLY_CUDA(cudaMemset(base, 0, flags_bytes + recv_bytes));
+  BFLY_TRY(dev_alloc(this, &ar_step, 1, &workspace_bytes));
+  BFLY_CUDA(cudaMemset(ar_step, 0, sizeof(unsigned)));
+  cudaIpcMemHandle_t mine;
+  BFLY_CUDA(cudaIpcGetMemHandle(&mine, base));
+  char *h_dev = nullptr, *all_dev = nullptr;
+  BFLY_TRY(dev_alloc(this, &h_dev, sizeof(mine), &workspace_bytes));
+  BFLY_TRY(dev_alloc(this, &all_dev, sizeof(mine) * tp, &workspace_bytes));
+  BFLY_CUDA(cudaMemcpy(h_dev, &mine, sizeof(mine), cudaMemcpyHostToDevice));
+  BFLY_CUDA(cudaDeviceSynchronize());                         // the zeroed buffer is in place before anyone can push
+  BFLY_TRY(all_gather_bytes(h_dev, all_dev, sizeof(mine)));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  std::vector<cudaIpcMemHandle_t> all((size_t)tp);
+  BFLY_CUDA(cudaMemcpy(all.data(), all_dev, sizeof(mine) * tp, cudaMemcpyDeviceToHost));
+  ar.tp = tp; ar.rank = d.rank; ar.max_rows = max_rows;
+  for (int r = 0; r < tp; ++r) {
+    char* p = base;
+    if (r != d.rank) {
+      void* q = nullptr;
+      BFLY_CUDA(cudaIpcOpenMemHandle(&q, all[(size_t)r], cudaIpcMemLazyEnablePeerAccess));
+      ipc_opened.push_back(q);
+      p = (char*)q;
+    }
+    ar.flags[r] = (unsigned*)p;
+    ar.recv[r] = (float*)(p + flags_bytes);
+  }
+  // nobody starts pushing before every rank has mapped its peers
+  BFLY_TRY(all_gather_bytes(h_dev, all_dev, sizeof(mine)));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  p2p_ready = true;
   return BFLY_OK;
 }
 
@@ -370,9 +414,14 @@ int Engine::gemm_swiglu(const bf16* W, const bf16* X, int N) {
 }
 
 // Row-parallel output: fold slices and all-reduce when tp > 1; tells the consumer where to read.
-int Engine::row_parallel_finish(int T, int slices, const float** src, int* n_partials) {
+int Engine::row_parallel_finish(int T, int slices, bool allow_fused, const float** src, int* n_partials, bool* fused) {
   const int h = d.hidden;
+  *fused = false;
   if (d.tp == 1) { *src = ws; *n_partials = slices; return BFLY_OK; }
+  if (allow_fused && p2p_ready && T <= ar.max_rows) {      // decode: the consumer kernel does the all-reduce
+    *src = ws; *n_partials = slices; *fused = true;
+    return BFLY_OK;
+  }
   float* buf = ws;
   if (slices > 1) {
     BFLY_TRY(launch_reduce_partials(ws, slices, (int64_t)T * h, red, (int64_t)T * h, stream));
@@ -381,6 +430,19 @@ int Engine::row_parallel_finish(int T, int slices, const float** src, int* n_par
   BFLY_TRY(all_reduce_f32(buf, (size_t)T * h));
   *src = buf; *n_partials = 1;
   return BFLY_OK;
+}
+
+// residual += (all-reduced) row-parallel output + bias; xn = norm(residual)
+int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,
+                       const bf16* beta) {
+  const int h = d.hidden;
+  const int ln = d.family == BFLY_FAMILY_GPT2;
+  if (fused) {
+    const int idx = (*ar_call)++;
+    return launch_ar_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, ar, idx,
+                              ar_step, 2 * d.n_layers, stream);
+  }
+  return launch_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, stream);
 }
 
 int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_logits, bool record_history) {
@@ -394,14 +456,15 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
   BFLY_TRY(launch_embed(tokens_dev, embed, pos_embed, lens, S, residual, T, h, c.vocab, keys, nb,
                         record_history ? history : nullptr, step_counter, stream));
   const float* pend_src = nullptr;
-  int pend_n = 0;
+  int pend_n = 0, ar_call = 0;
+  bool pend_fused = false, any_fused = false;
+  const bool allow_fused = (S == 1);
   const bf16* pend_bias = nullptr;
   for (int l = 0; l < c.n_layers; ++l) {
     const LayerW& w = layers[l];
     KvLayout kv{kv_pages + (int64_t)l * layer_kv_elems, table, pages_per_seq, c.page_size, kv_local, dh};
     int s = 1;
-    BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, pend_bias, w.attn_norm_w, w.attn_norm_b,
-                             c.norm_eps, ln, xn, T, h, stream));
+    BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, w.attn_norm_w, w.attn_norm_b));
     BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s));
     BFLY_TRY(launch_rope_kv(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, lens, S, T, q_local, kv_local, q, kv,
                             stream));
@@ -410,9 +473,9 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     else
       BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
     BFLY_TRY(gemm(w.wo, attn_out, q_local * dh, h, T, q_local * dh, &s));
-    BFLY_TRY(row_parallel_finish(T, s, &pend_src, &pend_n));
-    BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, w.bo, w.ffn_norm_w, w.ffn_norm_b, c.norm_eps,
-                             ln, xn, T, h, stream));
+    BFLY_TRY(row_parallel_finish(T, s, allow_fused, &pend_src, &pend_n, &pend_fused));
+    any_fused |= pend_fused;
+    BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, w.bo, w.ffn_norm_w, w.ffn_norm_b));
     if (c.n_experts)
       BFLY_TRY(launch_moe_router(xn, w.router, T, h, c.n_experts, c.top_k, c.rank * experts_local, experts_local,
                                  route_w, stream));
@@ -426,11 +489,11 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
                           f_block, c.n_experts ? route_w : nullptr, act, T, stream));
     }
     BFLY_TRY(gemm(w.w_down, act, ffn_act_cols, h, T, ffn_act_cols, &s));
-    BFLY_TRY(row_parallel_finish(T, s, &pend_src, &pend_n));
+    BFLY_TRY(row_parallel_finish(T, s, allow_fused, &pend_src, &pend_n, &pend_fused));
+    any_fused |= pend_fused;
     pend_bias = w.b_down;
   }
-  BFLY_TRY(launch_add_norm(residual, pend_src, pend_n, (int64_t)T * h, pend_bias, final_norm_w, final_norm_b,
-                           c.norm_eps, ln, xn, T, h, stream));
+  BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, final_norm_w, final_norm_b));
   // LM head on the last position of each sequence (row pitch S*h picks rows b*S + S-1)
   int s = 1;
   if (v_local > 0) {
@@ -445,7 +508,7 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
   } else {
     BFLY_TRY(launch_pick_tokens_pitched(keys, 1, d.max_batch, nb, cur_tokens + seq0, stream));
   }
-  BFLY_TRY(launch_advance(lens, nb, S, record_history ? step_counter : nullptr, stream));
+  BFLY_TRY(launch_advance(lens, nb, S, record_history ? step_counter : nullptr, any_fused ? ar_step : nullptr, stream));
   return BFLY_OK;
 }
 

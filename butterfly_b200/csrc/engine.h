@@ -71,6 +71,12 @@ struct Engine {
   uint64_t weight_bytes = 0, kv_bytes = 0, workspace_bytes = 0;
 
   void* comm = nullptr;                   // ncclComm_t
+  // decode-time all-reduce over peer memory (allreduce_norm.cu)
+  ArPeers ar{};
+  bool p2p_ready = false;
+  unsigned* ar_step = nullptr;
+  std::vector<void*> ipc_opened;
+  int p2p_init();
   std::map<int, GraphEntry> graphs;       // key = B*2 + want_logits
   int last_graph_nodes = 0;
 
@@ -96,7 +102,9 @@ struct Engine {
   int check_ready(int B);
   int gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out);
   int gemm_swiglu(const bf16* W, const bf16* X, int N);
-  int row_parallel_finish(int T, int splits, const float** src, int* n_partials);
+  int row_parallel_finish(int T, int splits, bool allow_fused, const float** src, int* n_partials, bool* fused);
+  int norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,
+                 const bf16* beta);
   int all_reduce_f32(float* buf, size_t count);
   int all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank);
   int forward(const int* tokens_dev, int seq0, int nb, int S, bool want_logits, bool record_history);

@@ -397,7 +397,7 @@ GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual) 
   // tools/tune_kernels.py: one wave of ~2 CTAs/SM beats any multi-wave split for these shapes.)
   int splits = 1;
   if (base < 2 * sm_count) {
-    splits = std::max(1, (2 * sm_count + base / 2) / base);
+    splits = std::max(1, (2 * sm_count) / base);          // never more CTAs than ~2 per SM: a second wave costs more
     splits = std::min(splits, std::max(1, nkb / 4));
     splits = std::min(splits, std::max(1, max_splits));
   }

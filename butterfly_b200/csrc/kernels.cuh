@@ -60,11 +60,23 @@ int launch_lm_finalize(const float* partials, int n_partials, int64_t partial_st
                        int v0, float* logits, int64_t logits_ld, unsigned long long* keys, cudaStream_t stream);
 int launch_pick_tokens_pitched(const unsigned long long* keys, int n_ranks, int pitch, int T, int* tokens_out,
                                cudaStream_t stream);
-int launch_advance(int* seq_lens, int B, int S, int* step_counter, cudaStream_t stream);
+int launch_advance(int* seq_lens, int B, int S, int* step_counter, unsigned* ar_step, cudaStream_t stream);
 int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_experts, int top_k,
                       int first_local, int n_local, float* route_w, cudaStream_t stream);
 int launch_reduce_partials(const float* partials, int n_partials, int64_t partial_stride, float* out,
                            int64_t count, cudaStream_t stream);
+
+// allreduce_norm.cu -- decode-time all-reduce over NVLink peer memory fused with residual add + norm
+constexpr int kMaxPeers = 8;
+struct ArPeers {
+  float* recv[kMaxPeers];        // rank r's receive buffer [2 parities][tp][max_rows][h] fp32 (peer-mapped)
+  unsigned* flags[kMaxPeers];    // rank r's epoch flags    [2 parities][tp][max_rows]
+  int tp, rank, max_rows;
+};
+int launch_ar_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
+                       const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
+                       int T, int h, const ArPeers& peers, int call_idx, const unsigned* step_ptr, int calls_per_step,
+                       cudaStream_t stream);
 
 // attn_decode.cu -- paged-KV attention, one query token per (virtual) sequence, split over the context
 int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count);
