@@ -91,7 +91,7 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the oracle on the host cores, bounded sample
 # --------------------------------------------------------------------------------------------------
-def cpu_decode_sample(n_layers_sample: int = 2, steps: int = 2, ctx: int = CTX, batch: int = BATCH):
+def cpu_decode_sample(n_layers_sample: int = 4, steps: int = 3, ctx: int = CTX, batch: int = BATCH):
     """Times the oracle's decode step at full Llama-3-8B width on `n_layers_sample` of the 32 layers
     plus the LM head, with a KV cache of `ctx` tokens per sequence already in place, and scales the
     layer part to 32 layers.  Returns (tokens/s extrapolated, description, cores)."""
@@ -288,7 +288,11 @@ def run_gpu(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": gemm["gbs"], "peak": hbm_peak, "unit": "GB/s",
-                         "frac": gemm["gbs"] / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": gemm["gbs"] / hbm_peak,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the committed
+                         # `ncu --set full` capture (profiles/r01_ncu_full_gemm_attn.txt): 235.17 + 3.96 MB
+                         "traffic": 239129344 if (tp == 1 and cfg.n_layers == 32) else None,
+                         "traffic_source": "profiles/r01_ncu_full_gemm_attn.txt", "peak_source": peak_src,
                          "kernel": gemm["kernel"], "shape_MNK": gemm["shape"], "splits": gemm["splits"],
                          "kernel_ms": gemm["ms"], "algo_bytes_per_launch": gemm["algo_bytes"]},
             "step_roofline": {"algo_bytes_per_step_per_gpu": step_bytes, "achieved_gbs_per_gpu": step_bytes / ms_step / 1e6,
