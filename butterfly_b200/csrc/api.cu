@@ -1,5 +1,6 @@
 // extern "C" surface of libbutterfly_b200.so (declared in include/butterfly_b200.h).
 // Nothing here throws across the ABI: every entry catches and converts to a BFLY_E* code.
+#include <algorithm>
 #include <exception>
 
 #include "engine.h"
@@ -310,6 +311,12 @@ int bfly_k_gemm(const void* w_bf16, const void* x_bf16, int M, int N, int K, int
       p.cluster = (splits > 1 && splits <= 8 && p.bn <= 64) ? 1 : 0;
     }
     if (stages > 0) p.stages = stages;
+    if (p.splits != 1 || p.cluster || p.bn < 128 || p.bn % 32 != 0) { p.pair = 0; p.persistent = 0; }
+    if (bn > 0 || stages > 0) p.persistent = 0;          // explicit tile overrides address the one-tile-per-CTA kernel
+    if (stages <= 0) {                                   // the override may have changed the stage footprint
+      const size_t sb = 16384 + (size_t)(p.bn >> p.pair) * 128;
+      p.stages = std::max(2, std::min(p.stages, (int)((200 * 1024) / sb)));
+    }
     if (slices_written) *slices_written = gemm_slices(p);
     return launch_gemm(cb(w_bf16), cb(x_bf16), ldx, p, out_f32, split_stride, mb(out_bf16), ldc, as_stream(stream));
   });

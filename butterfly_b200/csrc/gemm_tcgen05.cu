@@ -21,115 +21,15 @@
 #include <cstdlib>
 #include <mutex>
 
-#include "kernels.cuh"
+#include "tcgen05_common.cuh"
 
 namespace bfly {
 
 namespace {
 
-constexpr int BM = 128;                 // weight rows per tile (UMMA M)
-constexpr int BK = 64;                  // K per stage: 64 bf16 = one 128-byte swizzle row
-constexpr int UMMA_K = 16;
-constexpr int kThreads = 192;
-constexpr uint32_t kABytes = BM * BK * 2;   // 16 KiB per stage
-constexpr int kMaxStages = 8;
-constexpr int kMaxCluster = 8;           // portable thread-block cluster size
-constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;   // L2 policy: stream (weights)
-constexpr uint64_t kEvictLast = 0x14F0000000000000ull;    // L2 policy: keep (activations)
-
-// ---- PTX wrappers ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-  return ok != 0;
-}
-// Bounded wait: a protocol bug must surface as a trap (launch error), never as a hung GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) __trap();
-  }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
-                                            uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
-}
-// K-major operand tile in shared memory, 128-byte swizzle: rows of 128 B, 8-row atoms 1024 B apart.
-__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t addr) {
-  return (uint64_t)((addr >> 4) & 0x3FFFu)        // start address, 16-byte units
-         | ((uint64_t)(1024u >> 4) << 32)         // stride byte offset between 8-row atoms
-         | (1ull << 46)                           // descriptor version (sm_100)
-         | (2ull << 61);                          // layout: SWIZZLE_128B
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-struct GemmArgs {
-  int M, N, K;                 // M = output features (dual: gated features), N = tokens
-  int bn, stages, splits;
-  int cluster;                 // 1: the `splits` CTAs along z form a cluster and reduce through DSMEM
-  int dual;                    // 1: two accumulators (gate, up) and a fused SwiGLU epilogue
-  int f_block, n_blocks;       // dual: W rows are n_blocks x [gate(f_block) | up(f_block)]
-  uint32_t tmem_cols;
-  float* out_f32;
-  bf16* out_bf16;
-  const float* route_w;        // dual + MoE: [N][n_blocks] routing weights (0 = not routed), else nullptr
-  int64_t split_stride;
-  int64_t ldc;
-};
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank) {
-  uint32_t remote;
-  float v;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
-  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
-  return v;
-}
-__device__ __forceinline__ float silu_mul(float g, float u) { return g / (1.0f + expf(-g)) * u; }
-
+// kPair is a compile-time switch: a kernel that contains cta_group::2 instructions can only be launched as
+// a cluster, so the single-CTA instantiation must not contain them.
+template <bool kPair>
 __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                            const __grid_constant__ CUtensorMap tmap_x,
                                                            const GemmArgs args) {
@@ -137,8 +37,11 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // SWIZZLE_128B tiles: 1 KiB aligned
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int stages = args.stages, bn = args.bn, dual = args.dual;
+  constexpr int pair = kPair ? 1 : 0;
+  const uint32_t cta_rank = pair ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0u;
   const uint32_t a_bytes = kABytes * (uint32_t)(1 + dual);
-  const uint32_t b_bytes = (uint32_t)bn * BK * 2;
+  const uint32_t b_bytes = (uint32_t)(bn >> pair) * BK * 2;       // pair: each CTA stages half of the tokens
   const uint32_t a_base = smem_base;
   const uint32_t b_base = smem_base + (uint32_t)stages * a_bytes;
   const uint32_t bar_base = b_base + (uint32_t)stages * b_bytes;           // 8-byte aligned by construction
@@ -156,7 +59,7 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
     m0 = blk * 2 * args.f_block + in_blk;
     m_up = m0 + args.f_block;
     feat0 = blk * args.f_block + in_blk;
-    feat_limit = (blk + 1) * args.f_block;
+    feat_limit = blk < args.n_blocks ? (blk + 1) * args.f_block : 0;     // padding tile of an odd pair: stores nothing
   }
   const int n0 = blockIdx.y * bn;
   const int nkb_total = (args.K + BK - 1) / BK;
@@ -169,19 +72,25 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
     for (int s = 0; s < stages; ++s) {
-      mbar_init(full_bar(s), 1);
+      mbar_init(full_bar(s), 1 + pair);           // pair: both CTAs' producers arrive on the leader's barrier
       mbar_init(empty_bar(s), 1);
     }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
-                 "r"(args.tmem_cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if constexpr (kPair) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                   "r"(args.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                   "r"(args.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (pair) cluster_sync_all(); else __syncthreads();   // pair: the peer's barriers must exist before its TMA signals them
   tcgen05_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
@@ -206,33 +115,50 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
       const uint32_t tx = a_bytes + b_bytes;
       // Weights never depend on earlier kernels: fill the whole ring with weight tiles BEFORE waiting
       // for the predecessor (programmatic dependent launch), then add the activation tiles.
+      auto load = [&](uint32_t dst, const CUtensorMap* map, int s, int k_elem, int row, uint64_t policy) {
+        if constexpr (kPair) tma_load_2d_pair(dst, map, full_bar(s), k_elem, row, policy);
+        else tma_load_2d(dst, map, full_bar(s), k_elem, row, policy);
+      };
+      auto arm = [&](int s) {      // the leader's barrier counts the bytes of both CTAs
+        if (leader) mbar_expect_tx(full_bar(s), tx << pair);
+        else mbar_arrive_remote(full_bar(s), 0u);
+      };
       auto load_a = [&](int i, int s) {
         const int k_elem = (kb_begin + i) * BK;
-        tma_load_2d(a_base + (uint32_t)s * a_bytes, &tmap_w, full_bar(s), k_elem, m0, kEvictFirst);
-        if (dual) tma_load_2d(a_base + (uint32_t)s * a_bytes + kABytes, &tmap_w, full_bar(s), k_elem, m_up, kEvictFirst);
+        load(a_base + (uint32_t)s * a_bytes, &tmap_w, s, k_elem, m0, kEvictFirst);
+        if (dual) load(a_base + (uint32_t)s * a_bytes + kABytes, &tmap_w, s, k_elem, m_up, kEvictFirst);
       };
+      const int n_load = n0 + (int)cta_rank * (bn >> 1);          // pair: this CTA's half of the token tile
       const int pre = min(stages, nkb);
       for (int i = 0; i < pre; ++i) {
-        mbar_expect_tx(full_bar(i), tx);
+        arm(i);
         load_a(i, i);
       }
       pdl_wait();
       for (int i = 0; i < pre; ++i)
-        tma_load_2d(b_base + (uint32_t)i * b_bytes, &tmap_x, full_bar(i), (kb_begin + i) * BK, n0, kEvictLast);
+        load(b_base + (uint32_t)i * b_bytes, &tmap_x, i, (kb_begin + i) * BK, n_load, kEvictLast);
       for (int i = pre; i < nkb; ++i) {
         const int s = i % stages;
         const uint32_t ph = (uint32_t)(i / stages) & 1u;
         mbar_wait(empty_bar(s), ph ^ 1u);
-        mbar_expect_tx(full_bar(s), tx);
+        arm(s);
         load_a(i, s);
-        tma_load_2d(b_base + (uint32_t)s * b_bytes, &tmap_x, full_bar(s), (kb_begin + i) * BK, n0, kEvictLast);
+        load(b_base + (uint32_t)s * b_bytes, &tmap_x, s, (kb_begin + i) * BK, n_load, kEvictLast);
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // instruction descriptor: D=f32, A=B=bf16, both K-major, N = bn, M = 128
+    if (lane == 0 && leader) {
+      // instruction descriptor: D=f32, A=B=bf16, both K-major, N = bn, M = 128 (256 for a CTA pair)
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) |
-                             ((uint32_t)(BM >> 4) << 24);
+                             ((uint32_t)((BM << pair) >> 4) << 24);
+      auto mma = [&](uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t acc) {
+        if constexpr (kPair) umma_bf16_pair(d_tmem, a_desc, b_desc, idesc, acc);
+        else umma_bf16(d_tmem, a_desc, b_desc, idesc, acc);
+      };
+      auto commit = [&](uint32_t bar) {
+        if constexpr (kPair) umma_commit_pair(bar);
+        else umma_commit(bar);
+      };
       for (int i = 0; i < nkb; ++i) {
         const int s = i % stages;
         const uint32_t ph = (uint32_t)(i / stages) & 1u;
@@ -243,18 +169,17 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k) {
           // advance 32 bytes (16 bf16) inside the 128-byte swizzle row: +2 in 16-byte units
-          umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((i | k) != 0));
+          mma(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), (uint32_t)((i | k) != 0));
         }
         if (dual) {
           const uint64_t du = umma_smem_desc(a_base + (uint32_t)s * a_bytes + kABytes);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_bf16(tmem_base + (uint32_t)bn, du + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
-                      (uint32_t)((i | k) != 0));
+            mma(tmem_base + (uint32_t)bn, du + (uint64_t)(2 * k), db + (uint64_t)(2 * k), (uint32_t)((i | k) != 0));
         }
-        umma_commit(empty_bar(s));         // frees the smem stage once these MMAs have read it
+        commit(empty_bar(s));              // frees the smem stage (in both CTAs of a pair) once these MMAs have read it
       }
-      umma_commit(tmem_full_bar);          // accumulators complete
+      commit(tmem_full_bar);               // accumulators complete
     }
   } else {
     pdl_wait();      // outputs alias scratch that an earlier consumer kernel may still be reading
@@ -264,8 +189,20 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
     const int ml = quarter * 32 + lane;                 // tile-local weight row
     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     if (!args.cluster) {
-      for (int c0 = 0; c0 < bn; c0 += 16) {
+      // 32 accumulator columns (and, in dual mode, the matching 32 of the second accumulator) per TMEM
+      // round trip: the tcgen05.ld latency is exposed once per chunk, so wide chunks keep the epilogue short
+      int c0 = 0;
+      for (; c0 + 32 <= bn; c0 += 32) {
         if (n0 + c0 >= args.N) break;                   // warp-uniform
+        uint32_t r[32], ru[32];
+        tmem_ld32(taddr + (uint32_t)c0, r);
+        if (dual) tmem_ld32(taddr + (uint32_t)(bn + c0), ru);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          store(n0 + c0 + j, ml, __uint_as_float(r[j]), dual ? __uint_as_float(ru[j]) : 0.f, (int)blockIdx.z);
+      }
+      if (c0 < bn && n0 + c0 < args.N) {                // bn % 32 == 16 tail
         uint32_t r[16], ru[16];
         tmem_ld16(taddr + (uint32_t)c0, r);
         if (dual) tmem_ld16(taddr + (uint32_t)(bn + c0), ru);
@@ -326,10 +263,231 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
     cluster_sync_all();            // nobody may exit while a peer still reads its shared memory
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (pair) { __syncwarp(); cluster_sync_all(); } else __syncthreads();
   if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(args.tmem_cols)
-                 : "memory");
+    if constexpr (kPair)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(args.tmem_cols)
+                   : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(args.tmem_cols)
+                   : "memory");
+  }
+}
+
+
+// -----------------------------------------------------------------------------------------------
+// Persistent variant for the tensor-bound regime (>= 128 tokens per tile): one CTA (pair) per SM (pair)
+// loops over (weight tile, token tile) units; the accumulator is DOUBLE-BUFFERED in tensor memory so the
+// epilogue of unit i (tcgen05.ld -> SwiGLU/convert -> global stores) overlaps the MMAs of unit i+1, and
+// the TMA ring runs ahead across unit boundaries.  Units are ordered token-tile-fastest, so the CTAs of
+// a wave share one weight tile through L2 and every weight byte leaves HBM once.
+// -----------------------------------------------------------------------------------------------
+constexpr int kPersistEpiWarps = 8;
+constexpr int kPersistThreads = 64 + 32 * kPersistEpiWarps;
+
+template <bool kPair>
+__global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmap_w,
+                                                                   const __grid_constant__ CUtensorMap tmap_x,
+                                                                   const GemmArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = args.stages, bn = args.bn, dual = args.dual;
+  constexpr int pair = kPair ? 1 : 0;
+  const uint32_t cta_rank = pair ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0u;
+  const uint32_t a_bytes = kABytes * (uint32_t)(1 + dual);
+  const uint32_t b_bytes = (uint32_t)(bn >> pair) * BK * 2;
+  const uint32_t a_base = smem_base;
+  const uint32_t b_base = smem_base + (uint32_t)stages * a_bytes;
+  const uint32_t bar_base = b_base + (uint32_t)stages * b_bytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * (uint32_t)s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (uint32_t)(kMaxStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (uint32_t)(2 * kMaxStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (uint32_t)(2 * kMaxStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 4);
+
+  const int n_groups = (int)gridDim.x >> pair;            // CTAs (or CTA pairs) in the grid
+  const int my_group = (int)blockIdx.x >> pair;
+  const int total_units = args.m_units * args.n_tiles;
+  const int nkb = (args.K + BK - 1) / BK;
+  const uint32_t acc_cols = (uint32_t)bn * (uint32_t)(1 + dual);
+
+  // unit -> tile geometry
+  struct Tile { int m0, m_up, feat0, feat_limit, blk, n0; };
+  auto tile_of = [&](int u) {
+    Tile t;
+    const int n_idx = u % args.n_tiles, m_tile = (u / args.n_tiles) * (1 + pair) + (int)cta_rank;
+    t.n0 = n_idx * bn;
+    t.m0 = m_tile * BM; t.m_up = 0; t.feat0 = t.m0; t.blk = 0; t.feat_limit = args.M;
+    if (dual) {
+      const int tiles_per_blk = (args.f_block + BM - 1) / BM;
+      t.blk = m_tile / tiles_per_blk;
+      const int in_blk = (m_tile - t.blk * tiles_per_blk) * BM;
+      t.m0 = t.blk * 2 * args.f_block + in_blk;
+      t.m_up = t.m0 + args.f_block;
+      t.feat0 = t.blk * args.f_block + in_blk;
+      t.feat_limit = t.blk < args.n_blocks ? (t.blk + 1) * args.f_block : 0;
+    }
+    return t;
+  };
+
+  pdl_trigger();
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(full_bar(s), 1 + pair);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), kPersistEpiWarps * (1 + pair));   // one arrival per epilogue warp of every CTA of the pair
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    if constexpr (kPair) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                   "r"(args.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                   "r"(args.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+  }
+  tcgen05_fence_before();
+  if (pair) cluster_sync_all(); else __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t tx = a_bytes + b_bytes;
+      auto load = [&](uint32_t dst, const CUtensorMap* map, int s, int k_elem, int row, uint64_t policy) {
+        if constexpr (kPair) tma_load_2d_pair(dst, map, full_bar(s), k_elem, row, policy);
+        else tma_load_2d(dst, map, full_bar(s), k_elem, row, policy);
+      };
+      auto arm = [&](int s) {
+        if (leader) mbar_expect_tx(full_bar(s), tx << pair);
+        else mbar_arrive_remote(full_bar(s), 0u);
+      };
+      int it = 0;
+      bool waited = false;
+      for (int u = my_group; u < total_units; u += n_groups) {
+        const Tile t = tile_of(u);
+        const int n_load = t.n0 + (int)cta_rank * (bn >> 1) * pair;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % stages;
+          const uint32_t ph = (uint32_t)(it / stages) & 1u;
+          mbar_wait(empty_bar(s), ph ^ 1u);
+          arm(s);
+          const int k_elem = kb * BK;
+          load(a_base + (uint32_t)s * a_bytes, &tmap_w, s, k_elem, t.m0, kEvictLast);
+          if (dual) load(a_base + (uint32_t)s * a_bytes + kABytes, &tmap_w, s, k_elem, t.m_up, kEvictLast);
+          if (!waited) { pdl_wait(); waited = true; }     // weights never depend on the previous kernel; tokens do
+          load(b_base + (uint32_t)s * b_bytes, &tmap_x, s, k_elem, n_load, kEvictLast);
+        }
+      }
+      if (!waited) pdl_wait();
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) |
+                             ((uint32_t)((BM << pair) >> 4) << 24);
+      auto mma = [&](uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t acc) {
+        if constexpr (kPair) umma_bf16_pair(d_tmem, a_desc, b_desc, idesc, acc);
+        else umma_bf16(d_tmem, a_desc, b_desc, idesc, acc);
+      };
+      auto commit = [&](uint32_t bar) {
+        if constexpr (kPair) umma_commit_pair(bar);
+        else umma_commit(bar);
+      };
+      int it = 0, ui = 0;
+      for (int u = my_group; u < total_units; u += n_groups, ++ui) {
+        const int acc = ui & 1;
+        mbar_wait(tempty_bar(acc), (((uint32_t)ui >> 1) & 1u) ^ 1u);     // epilogue has drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t d0 = tmem_base + (uint32_t)acc * acc_cols;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % stages;
+          mbar_wait(full_bar(s), (uint32_t)(it / stages) & 1u);
+          tcgen05_fence_after();
+          const uint64_t da = umma_smem_desc(a_base + (uint32_t)s * a_bytes);
+          const uint64_t db = umma_smem_desc(b_base + (uint32_t)s * b_bytes);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            mma(d0, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), (uint32_t)((kb | k) != 0));
+          if (dual) {
+            const uint64_t du = umma_smem_desc(a_base + (uint32_t)s * a_bytes + kABytes);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              mma(d0 + (uint32_t)bn, du + (uint64_t)(2 * k), db + (uint64_t)(2 * k), (uint32_t)((kb | k) != 0));
+          }
+          commit(empty_bar(s));
+        }
+        commit(tfull_bar(acc));
+      }
+    }
+  } else {
+    pdl_wait();
+    // 8 epilogue warps: two per TMEM lane quarter, each draining half of the token columns
+    const int quarter = warp & 3;
+    const int col_half = (warp - 2) >> 2;
+    const int ml = quarter * 32 + lane;
+    const int c_begin = col_half * (bn >> 1), c_end = c_begin + (bn >> 1);
+    int ui = 0;
+    for (int u = my_group; u < total_units; u += n_groups, ++ui) {
+      const Tile t = tile_of(u);
+      const int acc = ui & 1;
+      mbar_wait(tfull_bar(acc), ((uint32_t)ui >> 1) & 1u);
+      tcgen05_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * acc_cols;
+      const int feat = t.feat0 + ml;
+      const bool row_ok = feat < t.feat_limit;
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+        if (t.n0 + c0 >= args.N) break;
+        uint32_t r[32], ru[32];
+        tmem_ld32(taddr + (uint32_t)c0, r);
+        if (dual) tmem_ld32(taddr + (uint32_t)(bn + c0), ru);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int n = t.n0 + c0 + j;
+            if (n >= args.N) break;
+            const float g = __uint_as_float(r[j]);
+            if (dual) {
+              float y = silu_mul(g, __uint_as_float(ru[j]));
+              if (args.route_w != nullptr) y *= args.route_w[(int64_t)n * args.n_blocks + t.blk];
+              args.out_bf16[(int64_t)n * args.ldc + feat] = __float2bfloat16_rn(y);
+            } else if (args.out_f32 != nullptr) {
+              args.out_f32[(int64_t)n * args.ldc + feat] = g;
+            } else {
+              args.out_bf16[(int64_t)n * args.ldc + feat] = __float2bfloat16_rn(g);
+            }
+          }
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) {                                   // hand the accumulator back to the MMA issuer
+        if constexpr (kPair) mbar_arrive_remote(tempty_bar(acc), 0u);
+        else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty_bar(acc)) : "memory");
+      }
+    }
+  }
+  tcgen05_fence_before();
+  if (pair) { __syncwarp(); cluster_sync_all(); } else __syncthreads();
+  if (warp == 1) {
+    if constexpr (kPair)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(args.tmem_cols)
+                   : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(args.tmem_cols)
+                   : "memory");
   }
 }
 
@@ -341,9 +499,9 @@ EncodeTiledFn g_encode = nullptr;
 std::once_flag g_init_once;
 int g_init_rc = BFLY_OK;
 
-size_t smem_needed(int bn, int stages, int dual) {
-  return 1024 /*align slack*/ + (size_t)stages * (kABytes * (size_t)(1 + dual) + (size_t)bn * BK * 2) +
-         8 * (2 * kMaxStages + 2);
+size_t smem_needed(int bn, int stages, int dual, int pair) {
+  return 1024 /*align slack*/ + (size_t)stages * (kABytes * (size_t)(1 + dual) + (size_t)(bn >> pair) * BK * 2) +
+         8 * (2 * kMaxStages + 6);
 }
 
 int make_map(CUtensorMap* map, const bf16* ptr, int64_t rows, int cols, int64_t pitch, int box_rows) {
@@ -375,7 +533,13 @@ int gemm_init() {
       return;
     }
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
-    e = cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    e = cudaFuncSetAttribute(gemm_tn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error(std::string("gemm: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
       g_init_rc = BFLY_ECUDA;
@@ -421,11 +585,27 @@ GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual) 
     p.cluster = 1;
   }
   p.splits = splits;
-  const size_t stage_bytes = kABytes * (size_t)(1 + dual) + (size_t)p.bn * BK * 2;
+  // Tensor-bound regime (>= 128 tokens per tile, no split): pair adjacent weight tiles with cta_group::2 so
+  // each SM reads only half of the token tile from shared memory (a single CTA's 128x256 UMMA needs
+  // 192 B/clk of operand reads against 128 B/clk of shared-memory bandwidth).  BFLY_GEMM_PAIR=0 disables.
+  static const bool allow_pair = [] { const char* e = getenv("BFLY_GEMM_PAIR"); return !(e && e[0] == '0'); }();
+  p.pair = (allow_pair && splits == 1 && !p.cluster && p.bn >= 128 && p.bn % 32 == 0 && m_tiles >= 2) ? 1 : 0;
+  // ... and run it persistently with a double-buffered accumulator (2 x bn x (1+dual) <= 512 TMEM columns):
+  // token tiles of 256 (plain) / 128 (fused SwiGLU).  BFLY_GEMM_PERSISTENT=0 disables.
+  static const bool allow_persist = [] { const char* e = getenv("BFLY_GEMM_PERSISTENT"); return !(e && e[0] == '0'); }();
+  p.persistent = 0;
+  if (allow_persist && splits == 1 && !p.cluster && N >= 128) {
+    p.persistent = 1;
+    p.bn = dual ? 128 : std::min(256, ((N + 63) / 64) * 64);
+    p.pair = (allow_pair && m_tiles >= 2) ? 1 : 0;
+  }
+  const size_t stage_bytes = kABytes * (size_t)(1 + dual) + (size_t)(p.bn >> p.pair) * BK * 2;
   int stages = (p.bn <= 64) ? ((dual || p.cluster) ? 3 : 4) : (int)std::min<size_t>(kMaxStages, (200 * 1024) / stage_bytes);
+  static const int big_stages = [] { const char* e = getenv("BFLY_GEMM_STAGES_BIG"); return e ? atoi(e) : 0; }();
+  if (p.bn > 64 && big_stages > 0) stages = big_stages;         // experiment knob: 3 lets two pair-CTAs share an SM
   stages = std::max(2, std::min(stages, kMaxStages));
   p.stages = stages;
-  p.smem_bytes = smem_needed(p.bn, stages, dual);
+  p.smem_bytes = smem_needed(p.bn, stages, dual, p.pair);
   return p;
 }
 
@@ -450,28 +630,34 @@ int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& pl
     BFLY_CHECK((out.out_f32 != nullptr) != (out.out_bf16 != nullptr), "gemm: exactly one of out_f32 / out_bf16");
     BFLY_CHECK(out.out_bf16 == nullptr || single_output, "gemm: bf16 output needs one complete K sum");
   }
-  const size_t smem = smem_needed(plan.bn, plan.stages, dual);
+  const int pair = plan.pair ? 1 : 0;
+  BFLY_CHECK(!pair || (plan.splits == 1 && !plan.cluster && plan.bn % 32 == 0), "gemm: CTA pairs need splits == 1, bn % 32 == 0");
+  BFLY_CHECK(!plan.persistent || (plan.splits == 1 && !plan.cluster && plan.bn % 64 == 0 && 2 * plan.bn * (1 + dual) <= 512),
+             "gemm: the persistent kernel needs splits == 1, bn % 32 == 0 and two accumulators in 512 TMEM columns");
+  const size_t smem = smem_needed(plan.bn, plan.stages, dual, pair);
   BFLY_CHECK(smem <= 227 * 1024, "gemm: tile does not fit shared memory");
   BFLY_CHECK(!plan.cluster || (size_t)(1 + dual) * plan.bn * BM * 4 <= (size_t)plan.stages * kABytes * (1 + dual),
              "gemm: cluster reduction buffer does not fit the operand ring");
   CUtensorMap mw, mx;
   const int64_t w_rows = dual ? 2 * (int64_t)plan.M : plan.M;
   BFLY_TRY(make_map(&mw, W, w_rows, plan.K, plan.K, BM));
-  BFLY_TRY(make_map(&mx, X, plan.N, plan.K, ldx, plan.bn));
+  BFLY_TRY(make_map(&mx, X, plan.N, plan.K, ldx, plan.bn >> pair));
   GemmArgs a{};
   a.M = plan.M; a.N = plan.N; a.K = plan.K;
   a.bn = plan.bn; a.stages = plan.stages; a.splits = plan.splits;
   a.cluster = plan.cluster && plan.splits > 1 ? 1 : 0;
   a.dual = dual;
+  a.pair = pair;
   a.f_block = dual ? out.f_block : plan.M;
   a.n_blocks = dual ? out.n_blocks : 1;
   uint32_t cols = 32;
-  while ((int)cols < plan.bn * (1 + dual)) cols <<= 1;
+  while ((int)cols < plan.bn * (1 + dual) * (plan.persistent ? 2 : 1)) cols <<= 1;
   a.tmem_cols = cols;
   a.out_f32 = out.out_f32; a.out_bf16 = out.out_bf16; a.route_w = out.route_w;
   a.split_stride = out.split_stride; a.ldc = out.ldc;
   int m_tiles = ceil_div(plan.M, BM);
   if (dual) m_tiles = out.n_blocks * ceil_div(out.f_block, BM);
+  if (pair) m_tiles = (m_tiles + 1) & ~1;        // an odd last tile is paired with an all-out-of-range one
   dim3 grid(m_tiles, ceil_div(plan.N, plan.bn), plan.splits);
 
   cudaLaunchConfig_t cfg{};
@@ -483,15 +669,30 @@ int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& pl
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.numAttrs = 1;
-  if (a.cluster) {
+  if (a.cluster || pair) {
     attr[1].id = cudaLaunchAttributeClusterDimension;
-    attr[1].val.clusterDim.x = 1;
+    attr[1].val.clusterDim.x = pair ? 2 : 1;
     attr[1].val.clusterDim.y = 1;
-    attr[1].val.clusterDim.z = plan.splits;
+    attr[1].val.clusterDim.z = pair ? 1 : plan.splits;
     cfg.numAttrs = 2;
   }
   cfg.attrs = attr;
-  BFLY_CUDA(cudaLaunchKernelEx(&cfg, gemm_tn_kernel, mw, mx, a));
+  if (plan.persistent) {
+    int dev = 0, sms = 148;
+    BFLY_CUDA(cudaGetDevice(&dev));
+    BFLY_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    a.m_units = m_tiles >> pair;
+    a.n_tiles = ceil_div(plan.N, plan.bn);
+    const int groups = std::min(a.m_units * a.n_tiles, sms >> pair);
+    cfg.gridDim = dim3((unsigned)(groups << pair), 1, 1);
+    cfg.blockDim = dim3(kPersistThreads);
+    if (pair) BFLY_CUDA(cudaLaunchKernelEx(&cfg, gemm_persistent_kernel<true>, mw, mx, a));
+    else BFLY_CUDA(cudaLaunchKernelEx(&cfg, gemm_persistent_kernel<false>, mw, mx, a));
+  } else if (pair) {
+    BFLY_CUDA(cudaLaunchKernelEx(&cfg, gemm_tn_kernel<true>, mw, mx, a));
+  } else {
+    BFLY_CUDA(cudaLaunchKernelEx(&cfg, gemm_tn_kernel<false>, mw, mx, a));
+  }
   count_launch();
   return BFLY_OK;
 }

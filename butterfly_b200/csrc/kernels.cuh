@@ -94,6 +94,8 @@ struct GemmPlan {
   int splits;           // split-K factor
   int cluster;          // 1: the K-slices form a thread-block cluster and are reduced through DSMEM into ONE
                         //    output (deterministic, rank order); 0: each slice is written to out + s * split_stride
+  int pair;             // 1: cta_group::2 CTA pairs (tensor-bound regime)
+  int persistent;       // 1: persistent kernel with a double-buffered TMEM accumulator (tensor-bound regime)
   int dual;             // 1: W = n_blocks x [gate(f_block) | up(f_block)] rows, fused SwiGLU epilogue (bf16 out)
   int stages;
   size_t smem_bytes;

@@ -119,6 +119,7 @@ GEMM_SHAPES = [
     # M (weight rows), N (tokens), K
     (128, 16, 64), (256, 32, 256), (384, 32, 4096), (1000, 7, 768), (6144, 32, 4096), (4096, 32, 1792),
     (500, 100, 520), (256, 300, 1024), (3072, 64, 768), (128, 1, 8192), (2048, 512, 512),
+    (4096, 2048, 512), (1152, 1000, 320),      # persistent kernel: several units per CTA pair, odd tile counts
 ]
 
 
@@ -142,7 +143,8 @@ def test_gemm_split_slices(lib, cuda, M, N, K):
 
 @pytest.mark.parametrize("N,K,n_blocks,fb,splits,routed", [
     (32, 1024, 1, 512, 1, False), (32, 4096, 1, 1792, 4, False), (32, 2048, 1, 256, 8, False), (7, 512, 3, 200, 2, True),
-    (300, 1024, 1, 384, 1, False), (64, 768, 2, 128, 3, True), (20, 4096, 1, 3584, 0, False)])
+    (300, 1024, 1, 384, 1, False), (64, 768, 2, 128, 3, True), (20, 4096, 1, 3584, 0, False),
+    (1500, 512, 1, 2048, 0, False), (700, 256, 3, 200, 0, True)])      # persistent dual kernel
 def test_gemm_fused_swiglu(lib, cuda, N, K, n_blocks, fb, splits, routed):
     """gate/up projection with the SwiGLU (and MoE routing weight) in the epilogue; splits > 1 reduces the
     K-slices inside a thread-block cluster through distributed shared memory."""
