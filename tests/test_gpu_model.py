@@ -126,6 +126,46 @@ def test_mixtral_8x7b_width_shallow_parity(cuda):
     _run_parity(MIXTRAL_8X7B.with_layers(1), B=3, S=20, n_steps=2, device_synth=True)
 
 
+@pytest.mark.parametrize("B,S,max_tokens", [(1, 1, None), (2, 33, None), (5, 31, 64), (3, 97, 128), (1, 200, None)])
+def test_prefill_edge_shapes_and_chunking(cuda, B, S, max_tokens):
+    """Ragged / minimal shapes: one-token prompts, prompts that are not a multiple of the 32-token tile or page,
+    and prefill split into several chunks of sequences (max_tokens < B*S)."""
+    from butterfly_b200 import Model
+    cfg = tiny("llama")
+    plan = make_plan(cfg, 1)
+    src = SyntheticSource(cfg, 0)
+    om = OracleModel(plan, [shard_weights(src, plan, 0)])
+    gm = Model(plan, 0, src, max_batch=B, max_ctx=S + 8, max_tokens=max_tokens)
+    toks = synthetic_tokens(cfg, B, S)
+    lo, lg = om.prefill(toks), gm.prefill(toks)
+    worst = (lo - lg).abs().max().item()
+    for _ in range(5):
+        t = ops.argmax(lo)
+        lo, lg = om.decode(t), gm.decode(t)
+        worst = max(worst, (lo - lg).abs().max().item())
+    gm.close()
+    assert worst <= LOGIT_TOL, worst
+
+
+def test_partial_batch_and_reprefill(cuda):
+    """A context sized for 8 sequences serves batches of 3 and 8, and a second prefill restarts the cache."""
+    from butterfly_b200 import Model
+    cfg = tiny("mixtral")
+    plan = make_plan(cfg, 1)
+    src = SyntheticSource(cfg, 0)
+    om = OracleModel(plan, [shard_weights(src, plan, 0)])
+    gm = Model(plan, 0, src, max_batch=8, max_ctx=96)
+    for B, S in ((3, 40), (8, 17), (3, 64)):
+        toks = synthetic_tokens(cfg, B, S, seed=B * 100 + S)
+        lo, lg = om.prefill(toks), gm.prefill(toks)
+        assert (lo - lg).abs().max().item() <= LOGIT_TOL
+        for _ in range(3):
+            t = ops.argmax(lo)
+            lo, lg = om.decode(t), gm.decode(t)
+            assert (lo - lg).abs().max().item() <= LOGIT_TOL
+    gm.close()
+
+
 def test_against_committed_golden_vectors(cuda):
     """GPU path vs the frozen oracle outputs in tests/golden/ (no oracle code involved at run time)."""
     import os
