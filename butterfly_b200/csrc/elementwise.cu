@@ -153,10 +153,24 @@ __global__ void rope_kv_kernel(const float* __restrict__ qkv, int n_partials, in
   const int ld = (nq + 2 * nk) * d;
   const int c0 = head * d + i, c1 = c0 + half;
   float x0 = 0.f, x1 = 0.f;
-  for (int p = 0; p < n_partials; ++p) {
-    const float* src = qkv + p * partial_stride + (int64_t)t * ld;
-    x0 += src[c0];
-    x1 += src[c1];
+  {
+    // slices are folded in index order, four pairs of loads in flight at a time (latency bound)
+    const float* src = qkv + (int64_t)t * ld;
+    int p = 0;
+    for (; p + 4 <= n_partials; p += 4) {
+      float a[4], b2[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k] = src[(p + k) * partial_stride + c0];
+        b2[k] = src[(p + k) * partial_stride + c1];
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { x0 += a[k]; x1 += b2[k]; }
+    }
+    for (; p < n_partials; ++p) {
+      x0 += src[p * partial_stride + c0];
+      x1 += src[p * partial_stride + c1];
+    }
   }
   if (bias != nullptr) {
     x0 += __bfloat162float(bias[c0]);
@@ -308,7 +322,21 @@ __global__ void act_kernel(const float* __restrict__ in, int n_partials, int64_t
     const int ld = 2 * f_out;
     const int64_t off_g = (int64_t)t * ld + (int64_t)blk * 2 * f_block + jj;
     float4 g = make_float4(0.f, 0.f, 0.f, 0.f), u = g;
-    for (int p = 0; p < n_partials; ++p) {
+    int p = 0;
+    for (; p + 4 <= n_partials; p += 4) {          // index order, four slice pairs in flight
+      float4 a[4], b[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k] = *reinterpret_cast<const float4*>(in + (p + k) * partial_stride + off_g);
+        b[k] = *reinterpret_cast<const float4*>(in + (p + k) * partial_stride + off_g + f_block);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        g.x += a[k].x; g.y += a[k].y; g.z += a[k].z; g.w += a[k].w;
+        u.x += b[k].x; u.y += b[k].y; u.z += b[k].z; u.w += b[k].w;
+      }
+    }
+    for (; p < n_partials; ++p) {
       const float4 a = *reinterpret_cast<const float4*>(in + p * partial_stride + off_g);
       const float4 b = *reinterpret_cast<const float4*>(in + p * partial_stride + off_g + f_block);
       g.x += a.x; g.y += a.y; g.z += a.z; g.w += a.w;
