@@ -33,6 +33,8 @@ UNIT = "tokens/s"
 BATCH = 32
 CTX = 2048
 WORKLOAD = "llama3-8b bf16 greedy decode, batch 32, ctx 2048 (BASELINE.json configs[1]/[2])"
+# --model selects another BASELINE.json shape (not the headline line): name -> (batch, ctx)
+OTHER_WORKLOADS = {"llama3-70b": (64, 4096), "mixtral-8x7b": (32, 2048), "gpt2-small": (1, 64)}
 
 
 def peaks():
@@ -206,7 +208,14 @@ def run_gpu(args):
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    cfg = LLAMA3_8B if args.layers <= 0 else LLAMA3_8B.with_layers(args.layers)
+    global BATCH, CTX, WORKLOAD
+    base_cfg = LLAMA3_8B
+    if args.model != "llama3-8b":
+        from butterfly_b200 import PRESETS
+        base_cfg = PRESETS[args.model]
+        BATCH, CTX = OTHER_WORKLOADS[args.model]
+        WORKLOAD = f"{args.model} bf16 greedy decode, batch {BATCH}, ctx {CTX} (BASELINE.json configs; not the headline line)"
+    cfg = base_cfg if args.layers <= 0 else base_cfg.with_layers(args.layers)
     tp = world if args.shard_of <= 1 else args.shard_of
     plan = make_plan(cfg, tp)
     W, K = args.warmup, args.steps
@@ -275,7 +284,8 @@ def run_gpu(args):
         value = BATCH * K / (ms / 1e3)
         ctx_mid = CTX + max(W, 3) + K / 2.0
         step_bytes = plan.weight_bytes_per_rank() + plan.kv_bytes_per_token_per_rank() * BATCH * (ctx_mid + 1)
-        gemm = measure_dominant_gemm(lib, plan.ffn_local * 2, BATCH, cfg.hidden)
+        gemm = measure_dominant_gemm(lib, plan.ffn_local * (2 if cfg.gated else 1) * max(1, plan.experts_local), BATCH,
+                                     cfg.hidden)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -303,7 +313,7 @@ def run_gpu(args):
         if args.shard_of > 1:
             line["INVALID"] = (f"profiling run: rank 0's shard of a tp={tp} plan on one GPU with the collectives "
                                "skipped; per-rank compute time only, results are not a model output")
-        if not args.no_cpu and world == 1 and args.shard_of <= 1:
+        if not args.no_cpu and world == 1 and args.shard_of <= 1 and args.model == "llama3-8b":
             v, sample, cores, _ = cpu_decode_sample()
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         print(json.dumps(line), flush=True)
@@ -321,6 +331,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layers", type=int, default=0, help="debug: reduce depth (the result is then NOT the headline config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--model", default="llama3-8b", choices=["llama3-8b", "llama3-70b", "mixtral-8x7b", "gpt2-small"],
+                    help="shape to run; anything but llama3-8b is an extra (non-headline) line")
     ap.add_argument("--shard-of", type=int, default=0, help="profiling aid: run rank 0's shard of a tp=N plan on one "
                     "GPU with the collectives skipped (the JSON line is marked INVALID)")
     args = ap.parse_args()

@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from butterfly_b200 import GPT2_SMALL, LLAMA3_8B, SyntheticSource, make_plan, shard_weights, synthetic_tokens, tiny
+from butterfly_b200 import GPT2_SMALL, LLAMA3_8B, LLAMA3_70B, MIXTRAL_8X7B, SyntheticSource, make_plan, shard_weights, synthetic_tokens, tiny
 from oracle import OracleModel, ops
 
 pytestmark = pytest.mark.gpu
@@ -83,3 +83,14 @@ def test_tp4_tiny(cuda, tmp_path):
 
 def test_tp8_mixtral_tiny_one_expert_per_rank(cuda, tmp_path):
     _run(tiny("mixtral", n_heads=8, n_kv_heads=8), 8, B=2, S=9, steps=3, tmp_path=tmp_path)
+
+
+def test_tp8_llama3_70b_width(cuda, tmp_path):
+    """BASELINE.json configs[3] shape at TP=8 (8 q heads + 1 kv head per rank), full width, depth 1: the fp32
+    oracle of all 80 layers would need 282 GB of host RAM."""
+    _run(LLAMA3_70B.with_layers(1), 8, B=4, S=70, steps=3, tmp_path=tmp_path)
+
+
+def test_tp8_mixtral_8x7b_width(cuda, tmp_path):
+    """BASELINE.json configs[4] shape at TP=8: one whole expert per rank, full width, depth 1."""
+    _run(MIXTRAL_8X7B.with_layers(1), 8, B=6, S=40, steps=3, tmp_path=tmp_path)
