@@ -147,6 +147,13 @@ def test_prefill_edge_shapes_and_chunking(cuda, B, S, max_tokens):
     assert worst <= LOGIT_TOL, worst
 
 
+def test_long_context_split_attention_parity(cuda):
+    """Context long enough (>= 512 tokens of capacity) that decode attention splits the context over several
+    CTAs and the last one to finish merges the splits (ticket path inside the engine)."""
+    _run_parity(tiny("llama"), B=2, S=300, n_steps=4, device_synth=True, max_ctx=640)
+    _run_parity(tiny("gpt2", max_pos=1024), B=1, S=530, n_steps=3, device_synth=True, max_ctx=1024)
+
+
 def test_partial_batch_and_reprefill(cuda):
     """A context sized for 8 sequences serves batches of 3 and 8, and a second prefill restarts the cache."""
     from butterfly_b200 import Model
