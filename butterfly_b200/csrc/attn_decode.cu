@@ -49,7 +49,9 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
 
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_trigger();
-  pdl_wait();                     // seq_lens, q and the cache are written by earlier kernels of the step
+  // Before the dependency on the predecessor (the RoPE / KV-append kernel) resolves, only state that
+  // older kernels finished long ago is touched: seq_lens (last written by the previous step) and cache
+  // tiles that do not contain the token being appended right now.
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r = lane >> 2, c = lane & 3;
   const int split = blockIdx.x, kvh = blockIdx.y, t = blockIdx.z;
@@ -92,8 +94,17 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
     bulk_copy_g2s(dst, kp, kBlockBytes, bar);
     bulk_copy_g2s(dst + kBlockBytes, vp, kBlockBytes, bar);
   };
-  if (lane == 0)
-    for (int i = 0; i < min(kStages, my_tiles); ++i) issue(i);
+  {
+    const int last_tile = n_tiles - 1;                 // holds this step's freshly appended K/V
+    const int n_pre = min(kStages, my_tiles);
+    if (lane == 0)
+      for (int i = 0; i < n_pre; ++i)
+        if (tile_begin + warp + i * kWarps != last_tile) issue(i);
+    pdl_wait();                                        // q and the new K/V row are ready from here on
+    if (lane == 0)
+      for (int i = 0; i < n_pre; ++i)
+        if (tile_begin + warp + i * kWarps == last_tile) issue(i);
+  }
 
   // Q as B fragments: head r (< G), the same d-permutation as the K chunks (chunk c of every 64 bytes)
   uint32_t qb[KSTEP_PAIRS][4];

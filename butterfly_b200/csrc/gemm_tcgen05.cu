@@ -134,6 +134,13 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
         arm(i);
         load_a(i, i);
       }
+      // ... and pull the next weight tiles into L2 while the predecessor (a small latency-bound kernel:
+      // norm, RoPE, activation) leaves HBM idle
+      const int pf_end = min(nkb, pre + args.l2_prefetch);
+      for (int i = pre; i < pf_end; ++i) {
+        tma_prefetch_l2_2d(&tmap_w, (kb_begin + i) * BK, m0);
+        if (dual) tma_prefetch_l2_2d(&tmap_w, (kb_begin + i) * BK, m_up);
+      }
       pdl_wait();
       for (int i = 0; i < pre; ++i)
         load(b_base + (uint32_t)i * b_bytes, &tmap_x, i, (kb_begin + i) * BK, n_load, kEvictLast);
@@ -648,6 +655,10 @@ int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& pl
   a.cluster = plan.cluster && plan.splits > 1 ? 1 : 0;
   a.dual = dual;
   a.pair = pair;
+  // Measured (8B, tp=1): 0 / 6 / 12 / 24 / 64 K-blocks of L2 prefetch give 4.72 / 4.72 / 4.79 / 4.87 / 5.01 ms
+  // per step -- the prefetch competes with the HBM-bound kernel it overlaps -- so it is off by default.
+  static const int l2pf = [] { const char* e = getenv("BFLY_GEMM_L2PF"); return e ? atoi(e) : 0; }();
+  a.l2_prefetch = plan.bn <= 64 ? l2pf : 0;          // weight-streaming regime only
   a.f_block = dual ? out.f_block : plan.M;
   a.n_blocks = dual ? out.n_blocks : 1;
   uint32_t cols = 32;

@@ -79,6 +79,10 @@ __device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a,
       "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// pull a weight tile into L2 without occupying shared memory (issued ahead of the PDL dependency)
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -127,6 +131,7 @@ struct GemmArgs {
   int pair;                    // 1: cta_group::2 -- two CTAs (adjacent weight tiles) share one 256 x bn UMMA, each
                                //    holding its own weight tile and HALF of the token tile in shared memory
   int f_block, n_blocks;       // dual: W rows are n_blocks x [gate(f_block) | up(f_block)]
+  int l2_prefetch;             // K-blocks beyond the ring to prefetch into L2 before the PDL dependency resolves
   int m_units, n_tiles;        // persistent kernel: (weight tile [pair]) x token tile units
   uint32_t tmem_cols;
   float* out_f32;
