@@ -233,6 +233,7 @@ def run_gpu(args):
         torch.cuda.synchronize()
 
     # ---- prefill of the 2048-token prompts (also reported) ----
+    model.prefill(toks[:1, :128].contiguous(), want_logits=False)      # warm-up: module load, NCCL channels
     barrier()
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     p0.record(stream)
