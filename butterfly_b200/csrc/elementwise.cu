@@ -130,7 +130,9 @@ int launch_add_norm(float* residual, const float* partials, int n_partials, int6
     BFLY_CUDA(cudaFuncSetAttribute(add_norm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     attr_set = true;
   }
-  const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
+  // few rows (decode): one wide CTA per row minimises latency; many rows (prefill): narrow CTAs keep many more
+  // rows in flight per SM
+  const int threads = T >= 512 ? 256 : std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
   BFLY_CUDA(launch_pdl(add_norm_kernel, dim3(T), dim3(threads), smem, stream, residual, partials, n_partials, partial_stride, bias, gamma, beta,
                                             eps, layer_norm, out, h));
   count_launch();
@@ -223,26 +225,42 @@ __global__ void __launch_bounds__(256) rope_kv_tile_kernel(
   const int n_tok = min(kRopeTile, S - s0);
   const int pos0 = seq_lens[b] + s0;
   const bool rotate = rope_table != nullptr && head < nq + nk;
-  for (int idx = threadIdx.x; idx < n_tok * half; idx += blockDim.x) {
-    const int tok = idx / half, i = idx - tok * half;
+  const int q4 = half >> 2;                            // float4 groups per half row (half % 4 == 0)
+#pragma unroll 2
+  for (int idx = threadIdx.x; idx < n_tok * q4; idx += blockDim.x) {
+    const int tok = idx / q4, i = (idx - tok * q4) * 4;
     const int c0 = head * d + i, c1 = c0 + half;
     const float* src = qkv + (int64_t)(b * S + s0 + tok) * ld;
-    float x0 = 0.f, x1 = 0.f;
-    for (int p = 0; p < n_partials; ++p) {
-      x0 += src[p * partial_stride + c0];
-      x1 += src[p * partial_stride + c1];
+    float4 a = *reinterpret_cast<const float4*>(src + c0), bb = *reinterpret_cast<const float4*>(src + c1);
+    for (int p = 1; p < n_partials; ++p) {
+      const float4 a2 = *reinterpret_cast<const float4*>(src + p * partial_stride + c0);
+      const float4 b2 = *reinterpret_cast<const float4*>(src + p * partial_stride + c1);
+      a.x += a2.x; a.y += a2.y; a.z += a2.z; a.w += a2.w;
+      bb.x += b2.x; bb.y += b2.y; bb.z += b2.z; bb.w += b2.w;
     }
+    float x0[4] = {a.x, a.y, a.z, a.w}, x1[4] = {bb.x, bb.y, bb.z, bb.w};
     if (bias != nullptr) {
-      x0 += __bfloat162float(bias[c0]);
-      x1 += __bfloat162float(bias[c1]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        x0[k] += __bfloat162float(bias[c0 + k]);
+        x1[k] += __bfloat162float(bias[c1 + k]);
+      }
     }
     if (rotate) {
-      const float2 cs = rope_table[(int64_t)(pos0 + tok) * half + i];
-      const float y0 = x0 * cs.x - x1 * cs.y, y1 = x1 * cs.x + x0 * cs.y;
-      x0 = y0; x1 = y1;
+      const float4* cs = reinterpret_cast<const float4*>(rope_table + (int64_t)(pos0 + tok) * half + i);
+      const float4 cs01 = cs[0], cs23 = cs[1];           // (cos, sin) of i, i+1 | i+2, i+3
+      const float cc[4] = {cs01.x, cs01.z, cs23.x, cs23.z}, sn[4] = {cs01.y, cs01.w, cs23.y, cs23.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float y0 = x0[k] * cc[k] - x1[k] * sn[k], y1 = x1[k] * cc[k] + x0[k] * sn[k];
+        x0[k] = y0; x1[k] = y1;
+      }
     }
-    tile[tok * ldt + i] = x0;
-    tile[tok * ldt + i + half] = x1;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      tile[tok * ldt + i + k] = x0[k];
+      tile[tok * ldt + i + half + k] = x1[k];
+    }
   }
   __syncthreads();
   if (head < nq) {
