@@ -47,7 +47,7 @@ typedef struct bfly_model_desc {
   int32_t max_pos;
   int32_t tied_head, bias;
   int32_t tp, rank;            /* tensor-parallel degree and this rank */
-  int32_t page_size;           /* tokens per KV page (power of two) */
+  int32_t page_size;           /* tokens per KV page (power of two >= 32; layout: butterfly_b200/kv_layout.py) */
   int32_t max_batch;           /* sequences resident in the KV cache */
   int32_t max_ctx;             /* KV capacity per sequence, tokens */
   int32_t max_tokens;          /* rows of one forward chunk (prefill is chunked to this) */
@@ -106,7 +106,10 @@ int bfly_sync(bfly_ctx* ctx);
 void* bfly_stream(bfly_ctx* ctx);        /* the ctx's cudaStream_t, for event timing by the caller */
 
 /* ---- per-kernel entry points on raw device pointers (parity tests, profiling) -------------- */
-/* All run on `stream` (a cudaStream_t, may be NULL = legacy default stream) and do not allocate. */
+/* All run on `stream` (a cudaStream_t, may be NULL = legacy default stream) and do not allocate.
+ * kv_pages_bf16 is one layer's cache [n_pages][2][kv_local][page_size*head_dim] in the engine's layout:
+ * K rows with the parity chunk swizzle, V transposed per 32-token block (csrc/kernels.cuh kv_k_offset /
+ * kv_v_offset, mirrored by butterfly_b200/kv_layout.py). */
 int bfly_k_fill_synth(void* dst_bf16, int64_t dst_pitch, uint64_t key, int64_t ncols_full, int64_t r0, int64_t c0,
                       int64_t rows, int64_t cols, float scale, float offset, void* stream);
 int bfly_k_embed(const int32_t* tokens, const void* table_bf16, const void* pos_table_bf16, const int32_t* seq_lens,
