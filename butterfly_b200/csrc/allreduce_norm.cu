@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
     }
     for (int r = 0; r < tp; ++r) *reinterpret_cast<float4*>(peers.recv[r] + slot_me * h + i) = v;
   }
-  __threadfence_system();
+  // The CTA barrier orders every thread's pushes before the flag stores below, and those are
+  // st.release at system scope (cumulative), so no per-thread system fence is needed.
   __syncthreads();
   // 2) publish the epoch flag at every rank, 3) wait for every rank's row
   if ((int)threadIdx.x < tp) st_release_sys_u32(peers.flags[threadIdx.x] + slot_me, epoch);
