@@ -52,7 +52,16 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
   for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
     const float* pp = partials + (int64_t)row * h + i;
     float4 v = *reinterpret_cast<const float4*>(pp);
-    for (int p = 1; p < n_partials; ++p) {
+    int p = 1;
+    for (; p + 4 <= n_partials; p += 4) {            // index order, four slices in flight
+      const float4 a0 = *reinterpret_cast<const float4*>(pp + (p + 0) * partial_stride);
+      const float4 a1 = *reinterpret_cast<const float4*>(pp + (p + 1) * partial_stride);
+      const float4 a2 = *reinterpret_cast<const float4*>(pp + (p + 2) * partial_stride);
+      const float4 a3 = *reinterpret_cast<const float4*>(pp + (p + 3) * partial_stride);
+      v.x = (((v.x + a0.x) + a1.x) + a2.x) + a3.x; v.y = (((v.y + a0.y) + a1.y) + a2.y) + a3.y;
+      v.z = (((v.z + a0.z) + a1.z) + a2.z) + a3.z; v.w = (((v.w + a0.w) + a1.w) + a2.w) + a3.w;
+    }
+    for (; p < n_partials; ++p) {
       const float4 a = *reinterpret_cast<const float4*>(pp + p * partial_stride);
       v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
     }
