@@ -393,18 +393,12 @@ int Engine::all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank) 
 }
 
 // ---- forward -----------------------------------------------------------------------------------
-int Engine::gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out, bool after_allreduce) {
+int Engine::gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out) {
   const GemmPlan p = gemm_plan(M, N, K, sm_count, kMaxSplits);
   const int slices = gemm_slices(p);
   if ((size_t)slices * N * M > ws_elems) { set_error("split-K scratch too small (internal sizing error)"); return BFLY_ESTATE; }
   *slices_out = slices;
-  GemmOut o{};
-  o.out_f32 = ws; o.split_stride = (int64_t)N * M; o.ldc = M;
-  // The fused all-reduce + norm kernel in front of this GEMM spends most of its time waiting on NVLink
-  // while HBM idles: let the GEMM's CTAs (already resident through PDL) pull their weights into L2 then.
-  static const int64_t pf_bytes = [] { const char* e = getenv("BFLY_AR_L2PF_MB"); return (int64_t)(e ? atoi(e) : 48) << 20; }();
-  o.l2_prefetch_bytes = after_allreduce ? (int)std::min<int64_t>(pf_bytes, (int64_t)M * K * 2) : 0;
-  return launch_gemm_ex(W, X, ldx, p, o, stream);
+  return launch_gemm(W, X, ldx, p, ws, (int64_t)N * M, nullptr, M, stream);
 }
 
 // gate/up projection with the SwiGLU (and the MoE routing weight) fused into the GEMM epilogue
@@ -471,7 +465,7 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     KvLayout kv{kv_pages + (int64_t)l * layer_kv_elems, table, pages_per_seq, c.page_size, kv_local, dh};
     int s = 1;
     BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, w.attn_norm_w, w.attn_norm_b));
-    BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s, pend_fused));
+    BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s));
     BFLY_TRY(launch_rope_kv(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, lens, S, T, q_local, kv_local, q, kv,
                             stream));
     if (S > 1)
@@ -490,7 +484,7 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     if (gated && fused_swiglu && T > 64) {
       BFLY_TRY(gemm_swiglu(w.w_in, xn, T));
     } else {
-      BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s, pend_fused));
+      BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s));
       BFLY_TRY(launch_act(ws, s, (int64_t)T * ffn_in_rows, w.b_up, gated ? ACT_SWIGLU : ACT_GELU_TANH, n_blocks,
                           f_block, c.n_experts ? route_w : nullptr, act, T, stream));
     }
@@ -503,7 +497,7 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
   // LM head on the last position of each sequence (row pitch S*h picks rows b*S + S-1)
   int s = 1;
   if (v_local > 0) {
-    BFLY_TRY(gemm(lm_head, xn + (int64_t)(S - 1) * h, (int64_t)S * h, v_local, nb, h, &s, pend_fused));
+    BFLY_TRY(gemm(lm_head, xn + (int64_t)(S - 1) * h, (int64_t)S * h, v_local, nb, h, &s));
     BFLY_TRY(launch_lm_finalize(ws, s, (int64_t)nb * v_local, nb, v_local, v0,
                                 want_logits ? logits + (int64_t)seq0 * v_shard : nullptr, v_shard, keys, stream));
   }

@@ -100,8 +100,7 @@ struct Engine {
  private:
   int find(const std::string& name, int64_t rows, int64_t cols, bool required, bf16** out);
   int check_ready(int B);
-  int gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out,
-           bool after_allreduce = false);
+  int gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out);
   int gemm_swiglu(const bf16* W, const bf16* X, int N);
   int row_parallel_finish(int T, int splits, bool allow_fused, const float** src, int* n_partials, bool* fused);
   int norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,

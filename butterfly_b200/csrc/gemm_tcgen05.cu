@@ -656,13 +656,10 @@ int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& pl
   a.dual = dual;
   a.pair = pair;
   // Measured (8B, tp=1): 0 / 6 / 12 / 24 / 64 K-blocks of L2 prefetch give 4.72 / 4.72 / 4.79 / 4.87 / 5.01 ms
-  // per step -- the prefetch competes with the HBM-bound kernel it overlaps -- so it is off by default.
+  // per step -- the prefetch competes with the HBM-bound kernel it overlaps -- so it is off by default; behind
+  // the cross-GPU all-reduce (tp=2 and tp=8, 0..96 MB) it made no measurable difference either.
   static const int l2pf = [] { const char* e = getenv("BFLY_GEMM_L2PF"); return e ? atoi(e) : 0; }();
   a.l2_prefetch = plan.bn <= 64 ? l2pf : 0;          // weight-streaming regime only
-  if (plan.bn <= 64 && out.l2_prefetch_bytes > 0) {
-    const int64_t ctas = (int64_t)ceil_div(plan.M, BM) * ceil_div(plan.N, plan.bn) * plan.splits;
-    a.l2_prefetch = (int)std::min<int64_t>(4096, out.l2_prefetch_bytes / (ctas * (int64_t)kABytes * (1 + dual)));
-  }
   a.f_block = dual ? out.f_block : plan.M;
   a.n_blocks = dual ? out.n_blocks : 1;
   uint32_t cols = 32;

@@ -107,8 +107,6 @@ struct GemmOut {
   int64_t ldc;
   int n_blocks, f_block;    // dual only
   const float* route_w;     // dual + MoE: [N][n_blocks], nullptr otherwise
-  int l2_prefetch_bytes;    // > 0: before the PDL dependency resolves, pull up to this many weight bytes (whole grid)
-                            // into L2 -- for a GEMM whose predecessor idles HBM (the cross-GPU all-reduce + norm)
 };
 int gemm_init();        // resolves cuTensorMapEncodeTiled, sets kernel attributes (once per process)
 GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual = 0);
