@@ -114,17 +114,16 @@ def cpu_decode_sample(n_layers_sample: int = 4, steps: int = 3, ctx: int = CTX, 
         t = base.repeat((n + base.numel() - 1) // base.numel())[:n].reshape(st.rows, st.cols)
         tensors[st.name] = t.reshape(-1) if st.cols == 1 else t
     om = OracleModel(plan, [RankWeights(plan, 0, tensors)])
-    for l in range(cfg.n_layers):
-        om.k_cache[l][0] = torch.randn((batch, ctx, cfg.n_kv_heads, cfg.head_dim), generator=g)
-        om.v_cache[l][0] = torch.randn((batch, ctx, cfg.n_kv_heads, cfg.head_dim), generator=g)
+    for l in range(cfg.n_layers):              # a cache of `ctx` tokens per sequence, with room to append
+        om.k_cache[l][0] = torch.randn((batch, ctx + 16, cfg.n_kv_heads, cfg.head_dim), generator=g)
+        om.v_cache[l][0] = torch.randn((batch, ctx + 16, cfg.n_kv_heads, cfg.head_dim), generator=g)
     om.pos = ctx
     tok = torch.randint(0, cfg.vocab, (batch,), generator=g, dtype=torch.int32)
     om.decode(tok)                             # warm-up
-    om.k_cache = [[k[0][:, :ctx]] for k in om.k_cache]
-    om.v_cache = [[v[0][:, :ctx]] for v in om.v_cache]
     om.pos = ctx
     t0 = time.perf_counter()
     for _ in range(steps):
+        om.pos = ctx                           # every timed step attends over exactly `ctx` cached tokens
         om.decode(tok)
     t_sample = (time.perf_counter() - t0) / steps
     # LM head + embedding share, timed separately so only the layer part is scaled

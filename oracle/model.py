@@ -52,6 +52,22 @@ class OracleModel:
         self.v_cache = [[None] * tp for _ in range(L)]
         self.pos = 0
 
+    def _append_kv(self, l, r, k, v):
+        """Append S new positions to the cache of (layer, rank) and return views of everything cached so far.
+        The cache grows geometrically, so a decode step copies only its own token, not the history."""
+        B, S = k.shape[0], k.shape[1]
+        buf_k, buf_v = self.k_cache[l][r], self.v_cache[l][r]
+        need = self.pos + S
+        if buf_k is None or buf_k.shape[1] < need:
+            cap = max(need, 2 * (buf_k.shape[1] if buf_k is not None else 0), 64)
+            nk_, nv_ = k.new_empty((B, cap) + k.shape[2:]), v.new_empty((B, cap) + v.shape[2:])
+            if buf_k is not None and self.pos > 0:
+                nk_[:, :self.pos], nv_[:, :self.pos] = buf_k[:, :self.pos], buf_v[:, :self.pos]
+            buf_k, buf_v = nk_, nv_
+            self.k_cache[l][r], self.v_cache[l][r] = buf_k, buf_v
+        buf_k[:, self.pos:need], buf_v[:, self.pos:need] = k, v
+        return buf_k[:, :need], buf_v[:, :need]
+
     def _all_reduce(self, parts):
         acc = ops.all_reduce_sum(parts)
         if self.dist is not None:
@@ -90,10 +106,7 @@ class OracleModel:
                     q, k = ops.rope(q, positions, cfg.rope_theta), ops.rope(k, positions, cfg.rope_theta)
                 q, k, v = rq(q), rq(k), rq(v)
                 k, v = k.reshape(B, S, nk, d), v.reshape(B, S, nk, d)
-                if self.k_cache[l][r] is not None:
-                    k = torch.cat([self.k_cache[l][r], k], dim=1)
-                    v = torch.cat([self.v_cache[l][r], v], dim=1)
-                self.k_cache[l][r], self.v_cache[l][r] = k, v
+                k, v = self._append_kv(l, r, k, v)
                 a = rq(ops.attention(q.reshape(B, S, nq, d), k, v, self.pos)).reshape(B * S, nq * d)
                 parts.append(ops.linear(a, w[p + "wo"]))
             x = x + self._all_reduce(parts)
