@@ -14,6 +14,9 @@ from .weights import (SyntheticSource, DictSource, RankWeights, shard_weights, s
                       synthetic_tokens)
 
 
+from .checkpoint import load_checkpoint, from_hf_state_dict  # noqa: F401,E402
+
+
 def __getattr__(name):
     if name == "Model":
         from .model import Model
