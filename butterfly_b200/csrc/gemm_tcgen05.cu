@@ -287,9 +287,11 @@ __global__ void __launch_bounds__(kThreads) gemm_tn_kernel(const __grid_constant
 // loops over (weight tile, token tile) units; the accumulator is DOUBLE-BUFFERED in tensor memory so the
 // epilogue of unit i (tcgen05.ld -> SwiGLU/convert -> global stores) overlaps the MMAs of unit i+1, and
 // the TMA ring runs ahead across unit boundaries.  Units are ordered token-tile-fastest, so the CTAs of
-// a wave share one weight tile through L2 and every weight byte leaves HBM once.
+// a wave share one weight tile through L2 and every weight byte leaves HBM once (see tile_of for the
+// 2D-blocked refinement that also keeps the token tiles L2-resident).
 // -----------------------------------------------------------------------------------------------
 constexpr int kPersistEpiWarps = 8;
+constexpr int kBandUnits = 8;             // weight units (CTA-pair tiles) per L2 band of the persistent schedule
 constexpr int kPersistThreads = 64 + 32 * kPersistEpiWarps;
 
 template <bool kPair>
@@ -324,7 +326,14 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
   struct Tile { int m0, m_up, feat0, feat_limit, blk, n0; };
   auto tile_of = [&](int u) {
     Tile t;
-    const int n_idx = u % args.n_tiles, m_tile = (u / args.n_tiles) * (1 + pair) + (int)cta_rank;
+    // 2D-blocked unit order: bands of kBandUnits weight units; inside a band the weight unit varies fastest,
+    // so a wave of ~74 units touches ~8 weight units x ~9 token tiles (both L2-resident) instead of
+    // re-streaming every token tile for each weight unit.
+    const int per_band = kBandUnits * args.n_tiles;
+    const int band = u / per_band, rem = u - band * per_band;
+    const int band_m = min(kBandUnits, args.m_units - band * kBandUnits);
+    const int n_idx = rem / band_m;
+    const int m_tile = (band * kBandUnits + (rem - n_idx * band_m)) * (1 + pair) + (int)cta_rank;
     t.n0 = n_idx * bn;
     t.m0 = m_tile * BM; t.m_up = 0; t.feat0 = t.m0; t.blk = 0; t.feat_limit = args.M;
     if (dual) {
