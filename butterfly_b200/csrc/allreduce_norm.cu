@@ -10,7 +10,17 @@
 // buffered by call parity and flags carry a monotonically increasing epoch, so nothing is ever reset.
 // A rank can be at most one call ahead of a peer (its next call needs that peer's flag), which is what
 // makes two parities sufficient.  Latency regime only (T <= max_batch rows); prefill keeps NCCL.
+//
+// Two modes.  ONE-SHOT (small rows, e.g. 32 x 4096): every rank pushes its row to all tp ranks -- one
+// NVLink hop, tp x the bytes.  TWO-SHOT (T*h*4 >= 1 MiB and tp >= 4, e.g. the 64 x 8192 rows of the 70B
+// shape, where one-shot spends ~38 us per call moving 14 MB per rank): row r is OWNED by rank r % tp;
+// the others push their partial row to the owner only, the owner sums in rank order and pushes the sum
+// back to everybody -- two hops, 2*(tp-1)/tp of a row per rank instead of tp-1 rows.  Both modes use the
+// same buffers: slot [parity][src][row] of the owner holds src's partial; slot [parity][owner][row] of a
+// non-owner (unused by the first hop) receives the reduced row.  Either way every rank adds the same
+// fp32 sum to its replicated residual, so the ranks stay bit-identical.
 #include <algorithm>
+#include <cstdlib>
 
 #include "kernels.cuh"
 
@@ -27,6 +37,14 @@ __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
   return v;
 }
 
+// spin until a peer has published this call's epoch; a lost peer must not hang the GPU
+__device__ __forceinline__ void wait_epoch(const unsigned* f, unsigned epoch) {
+  const long long t0 = clock64();
+  while (ld_acquire_sys_u32(f) != epoch) {
+    if (clock64() - t0 > 8000000000ll) __trap();
+  }
+}
+
 // the receive buffer is written by other GPUs: read it around L1
 __device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
   float4 v;
@@ -38,7 +56,7 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
     float* __restrict__ residual, const float* __restrict__ partials, int n_partials, int64_t partial_stride,
     const bf16* __restrict__ bias, const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float eps,
     int layer_norm, bf16* __restrict__ out, int h, ArPeers peers, int call_idx, const unsigned* __restrict__ step_ptr,
-    int calls_per_step) {
+    int calls_per_step, int two_shot) {
   extern __shared__ __align__(16) float srow[];
   __shared__ float red[32];
   pdl_trigger();
@@ -48,7 +66,10 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
   const int parity = call_idx & 1;
   const int64_t slot_me = ((int64_t)(parity * tp + me) * peers.max_rows + row);
 
-  // 1) fold this rank's slices of the row and push it to every rank (including this one)
+  const int owner = two_shot ? row % tp : -1;       // two-shot: the rank that reduces this row
+  const bool own = owner == me;
+
+  // 1) fold this rank's slices of the row; push it to every rank (one-shot) or to the row's owner
   for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
     const float* pp = partials + (int64_t)row * h + i;
     float4 v = *reinterpret_cast<const float4*>(pp);
@@ -65,21 +86,48 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
       const float4 a = *reinterpret_cast<const float4*>(pp + p * partial_stride);
       v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
     }
-    for (int r = 0; r < tp; ++r) *reinterpret_cast<float4*>(peers.recv[r] + slot_me * h + i) = v;
+    if (!two_shot) {
+      for (int r = 0; r < tp; ++r) *reinterpret_cast<float4*>(peers.recv[r] + slot_me * h + i) = v;
+    } else if (own) {
+      *reinterpret_cast<float4*>(srow + i) = v;      // the owner's own partial never leaves the SM
+    } else {
+      *reinterpret_cast<float4*>(peers.recv[owner] + slot_me * h + i) = v;
+    }
   }
   // The CTA barrier orders every thread's pushes before the flag stores below, and those are
   // st.release at system scope (cumulative), so no per-thread system fence is needed.
   __syncthreads();
-  // 2) publish the epoch flag at every rank, 3) wait for every rank's row
-  if ((int)threadIdx.x < tp) st_release_sys_u32(peers.flags[threadIdx.x] + slot_me, epoch);
-  if ((int)threadIdx.x < tp) {
-    const unsigned* f = peers.flags[me] + ((int64_t)(parity * tp + (int)threadIdx.x) * peers.max_rows + row);
-    const long long t0 = clock64();
-    while (ld_acquire_sys_u32(f) != epoch) {
-      if (clock64() - t0 > 8000000000ll) __trap();     // a lost peer must not hang the GPU
+  if (!two_shot) {
+    // 2) publish the epoch flag at every rank, 3) wait for every rank's row
+    if ((int)threadIdx.x < tp) st_release_sys_u32(peers.flags[threadIdx.x] + slot_me, epoch);
+    if ((int)threadIdx.x < tp) wait_epoch(peers.flags[me] + ((int64_t)(parity * tp + (int)threadIdx.x) * peers.max_rows + row), epoch);
+    __syncthreads();
+  } else if (own) {
+    // 2) wait for the tp-1 partial rows, 3) sum in rank order, push the sum to everybody
+    if ((int)threadIdx.x < tp && (int)threadIdx.x != me)
+      wait_epoch(peers.flags[me] + ((int64_t)(parity * tp + (int)threadIdx.x) * peers.max_rows + row), epoch);
+    __syncthreads();
+    for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < tp; ++r) {
+        const float4 x = r == me ? *reinterpret_cast<const float4*>(srow + i)
+                                 : ld_volatile_f4(peers.recv[me] + ((int64_t)(parity * tp + r) * peers.max_rows + row) * h + i);
+        a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+      }
+      *reinterpret_cast<float4*>(srow + i) = a;      // same thread read srow[i..i+3] above
+      for (int r = 0; r < tp; ++r)
+        if (r != me) *reinterpret_cast<float4*>(peers.recv[r] + slot_me * h + i) = a;
     }
+    __syncthreads();
+    if ((int)threadIdx.x < tp && (int)threadIdx.x != me) st_release_sys_u32(peers.flags[threadIdx.x] + slot_me, epoch);
+  } else {
+    // 2) tell the owner the partial row is there, 3) wait for the reduced row to come back
+    if (threadIdx.x == 0) {
+      st_release_sys_u32(peers.flags[owner] + slot_me, epoch);
+      wait_epoch(peers.flags[me] + ((int64_t)(parity * tp + owner) * peers.max_rows + row), epoch);
+    }
+    __syncthreads();
   }
-  __syncthreads();
 
   // 4) sum in rank order from local memory, residual add, norm
   float* res = residual + (int64_t)row * h;
@@ -87,9 +135,15 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
   for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
     float4 v = *reinterpret_cast<const float4*>(res + i);
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r = 0; r < tp; ++r) {
-      const float4 x = ld_volatile_f4(peers.recv[me] + ((int64_t)(parity * tp + r) * peers.max_rows + row) * h + i);
-      a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+    if (!two_shot) {
+      for (int r = 0; r < tp; ++r) {
+        const float4 x = ld_volatile_f4(peers.recv[me] + ((int64_t)(parity * tp + r) * peers.max_rows + row) * h + i);
+        a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+      }
+    } else if (own) {
+      a = *reinterpret_cast<const float4*>(srow + i);
+    } else {
+      a = ld_volatile_f4(peers.recv[me] + ((int64_t)(parity * tp + owner) * peers.max_rows + row) * h + i);
     }
     v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
     if (bias != nullptr) {
@@ -144,9 +198,12 @@ int launch_ar_add_norm(float* residual, const float* partials, int n_partials, i
     attr_set = true;
   }
   const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
+  // every rank takes the same branch: T, h and tp are identical across the group (and so must the knob be)
+  static const int forced = [] { const char* e = getenv("BFLY_AR_TWO_SHOT"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
+  const int two_shot = forced >= 0 ? forced : (peers.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
   BFLY_CUDA(launch_pdl(ar_add_norm_kernel, dim3(T), dim3(threads), smem, stream, residual, partials, n_partials,
                        partial_stride, bias, gamma, beta, eps, layer_norm, out, h, peers, call_idx, step_ptr,
-                       calls_per_step));
+                       calls_per_step, two_shot));
   count_launch();
   return BFLY_OK;
 }
