@@ -192,11 +192,11 @@ int launch_ar_add_norm(float* residual, const float* partials, int n_partials, i
   BFLY_CHECK(T > 0 && T <= peers.max_rows && h % 4 == 0 && h * 4 <= 160 * 1024, "ar_add_norm: bad shape");
   BFLY_CHECK(n_partials >= 1 && partials != nullptr && peers.tp >= 2 && peers.tp <= kMaxPeers, "ar_add_norm: bad peers");
   const size_t smem = (size_t)h * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr;
+  BFLY_TRY(attr.run([] {
     BFLY_CUDA(cudaFuncSetAttribute(ar_add_norm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    attr_set = true;
-  }
+    return (int)BFLY_OK;
+  }));
   const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
   // every rank takes the same branch: T, h and tp are identical across the group (and so must the knob be)
   static const int forced = [] { const char* e = getenv("BFLY_AR_TWO_SHOT"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();

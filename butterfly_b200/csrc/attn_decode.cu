@@ -264,12 +264,12 @@ __global__ void attn_combine_kernel(const float* __restrict__ part_o, const floa
 template <int D, int G>
 int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, int T, int nq, float* part_o,
                 float* part_ml, int n_splits, bf16* out, cudaStream_t stream) {
-  static bool attr_done = false;
+  static PerDeviceOnce attr;
   constexpr size_t smem = attn_smem_bytes<D>();
-  if (!attr_done) {
+  BFLY_TRY(attr.run([] {
     BFLY_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done = true;
-  }
+    return (int)BFLY_OK;
+  }));
   dim3 grid(n_splits, kv.kv_local, T);
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
   BFLY_CUDA(launch_pdl(attn_decode_kernel<D, G>, grid, dim3(kWarps * 32), smem, stream, q, kv, seq_lens, S, nq, part_o,

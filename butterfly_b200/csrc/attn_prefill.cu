@@ -232,12 +232,12 @@ __global__ void __launch_bounds__(kWarps * 32) attn_prefill_kernel(const bf16* _
 template <int D, int G>
 int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, int B, int nq, bf16* out,
                 cudaStream_t stream) {
-  static bool attr_done = false;
+  static PerDeviceOnce attr;
   constexpr size_t smem = prefill_smem_bytes<D>();
-  if (!attr_done) {
+  BFLY_TRY(attr.run([] {
     BFLY_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done = true;
-  }
+    return (int)BFLY_OK;
+  }));
   constexpr int QB = kCols / G;
   dim3 grid(ceil_div(S, QB), kv.kv_local, B);
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);

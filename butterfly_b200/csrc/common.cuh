@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
 #include <string>
 #include <utility>
 
@@ -38,6 +39,27 @@ void set_error(const std::string& msg);   // thread-local last error (api.cu)
     int _rc = (expr);             \
     if (_rc != 0) return _rc;     \
   } while (0)
+
+// Function attributes (cudaFuncSetAttribute) belong to a device, not to the process: a host that drives
+// several GPUs from one process must set them once on each.  run(fn) calls fn() the first time it is
+// reached with a given device current (and again if fn failed).
+struct PerDeviceOnce {
+  static constexpr int kMaxDevices = 64;
+  std::mutex mu;
+  bool done[kMaxDevices] = {};
+  template <class Fn>
+  int run(Fn&& fn) {
+    int dev = -1;
+    BFLY_CUDA(cudaGetDevice(&dev));
+    BFLY_CHECK(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!done[dev]) {
+      BFLY_TRY(fn());
+      done[dev] = true;
+    }
+    return BFLY_OK;
+  }
+};
 
 // Counts kernel launches made by this library (bench.py reports it as gpu_launches).
 extern unsigned long long g_launch_count;

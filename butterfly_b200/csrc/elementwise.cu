@@ -125,11 +125,11 @@ int launch_add_norm(float* residual, const float* partials, int n_partials, int6
   BFLY_CHECK(T > 0 && h % 4 == 0 && h * 4 <= 160 * 1024, "add_norm: T>0, h%4==0, h<=40960");
   BFLY_CHECK(n_partials == 0 || partials != nullptr, "add_norm: partials missing");
   const size_t smem = (size_t)h * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr;
+  BFLY_TRY(attr.run([] {
     BFLY_CUDA(cudaFuncSetAttribute(add_norm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    attr_set = true;
-  }
+    return (int)BFLY_OK;
+  }));
   // few rows (decode): one wide CTA per row minimises latency; many rows (prefill): narrow CTAs keep many more
   // rows in flight per SM
   const int threads = T >= 512 ? 256 : std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));

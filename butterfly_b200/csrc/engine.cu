@@ -11,6 +11,8 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <vector>
 
 namespace bfly {
@@ -30,7 +32,10 @@ struct NcclApi {
 };
 NcclApi g_nccl;
 
+std::mutex g_nccl_mutex;
+
 int load_nccl() {
+  std::lock_guard<std::mutex> lock(g_nccl_mutex);
   if (g_nccl.lib) return BFLY_OK;
   void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);   // the copy torch already loaded, if any
   if (!lib) {
@@ -101,7 +106,8 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   BFLY_CUDA(cudaSetDevice(device));
   BFLY_TRY(gemm_init());
 
-  Engine* e = new Engine();
+  std::unique_ptr<Engine> owner(new Engine());        // freed (with everything it allocated) on any early return
+  Engine* e = owner.get();
   e->d = c;
   e->device = device;
   cudaDeviceProp prop;
@@ -182,7 +188,7 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   A(dev_alloc(e, &e->cur_tokens, (size_t)maxB, wsb));
   A(dev_alloc(e, &e->history, (size_t)kMaxGreedySteps * maxB, wsb));
   if (c.rope_theta > 0.f) A(dev_alloc(e, &e->rope_table, (size_t)c.max_ctx * (c.head_dim / 2), wsb));
-  if (rc != BFLY_OK) { delete e; return rc; }
+  if (rc != BFLY_OK) return rc;
 
   // identity page table, zero lengths
   std::vector<int> table((size_t)e->n_pages);
@@ -207,11 +213,13 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     BFLY_CUDA(cudaMemcpy(e->rope_table, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
   }
   BFLY_CUDA(cudaHostAlloc((void**)&e->pinned, kPinnedBytes, cudaHostAllocDefault));
-  *out = e;
+  *out = owner.release();
   return BFLY_OK;
 }
 
 Engine::~Engine() {
+  cudaSetDevice(device);
+  if (stream) cudaStreamSynchronize(stream);
   for (auto& kv : graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : ipc_opened) cudaIpcCloseMemHandle(p);
@@ -572,8 +580,9 @@ int Engine::decode_graph(int B, bool want_logits, GraphEntry** out) {
   g_launch_count = before;                      // captured launches did not execute
   if (rc != BFLY_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
   BFLY_CUDA(ce);
-  BFLY_CUDA(cudaGraphInstantiate(&ge.exec, graph, 0));
+  const cudaError_t ie = cudaGraphInstantiate(&ge.exec, graph, 0);
   cudaGraphDestroy(graph);
+  BFLY_CUDA(ie);
   graphs[key] = ge;
   last_graph_nodes = ge.kernel_nodes;
   *out = &graphs[key];
@@ -623,7 +632,7 @@ int Engine::decode_greedy(int B, int n_steps, int32_t* tokens_out_host) {
 }
 
 int Engine::set_page_table(const int32_t* table_host, int n_seqs, int pps) {
-  BFLY_CHECK(n_seqs >= 1 && n_seqs <= d.max_batch && pps == pages_per_seq, "set_page_table: shape");
+  BFLY_CHECK(table_host != nullptr && n_seqs >= 1 && n_seqs <= d.max_batch && pps == pages_per_seq, "set_page_table: shape");
   std::vector<char> seen((size_t)n_pages, 0);
   for (int64_t i = 0; i < (int64_t)n_seqs * pps; ++i) {
     const int p = table_host[i];

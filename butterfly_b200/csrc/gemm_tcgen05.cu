@@ -549,19 +549,17 @@ int gemm_init() {
       return;
     }
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
-    e = cudaFuncSetAttribute(gemm_tn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_tn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(gemm_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) {
-      set_error(std::string("gemm: cudaFuncSetAttribute: ") + cudaGetErrorString(e));
-      g_init_rc = BFLY_ECUDA;
-    }
   });
-  return g_init_rc;
+  BFLY_TRY(g_init_rc);
+  static PerDeviceOnce attr;                       // the shared-memory opt-in is per device
+  return attr.run([] {
+    constexpr int kSmem = 227 * 1024;
+    BFLY_CUDA(cudaFuncSetAttribute(gemm_tn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    BFLY_CUDA(cudaFuncSetAttribute(gemm_tn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    BFLY_CUDA(cudaFuncSetAttribute(gemm_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    BFLY_CUDA(cudaFuncSetAttribute(gemm_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    return (int)BFLY_OK;
+  });
 }
 
 // M = output features (dual: gated features, i.e. half the weight rows).
