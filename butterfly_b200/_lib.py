@@ -47,6 +47,7 @@ SIGNATURES = {
     "bfly_comm_init": (i32, [vp, vp, i32, i32]),
     "bfly_set_page_table": (i32, [vp, vp, i32, i32]),
     "bfly_prefill": (i32, [vp, vp, i32, i32, vp, vp]),
+    "bfly_prefill_at": (i32, [vp, i32, vp, i32, i32, vp, vp]),
     "bfly_decode": (i32, [vp, vp, i32, vp, vp]),
     "bfly_decode_greedy": (i32, [vp, i32, i32, vp]),
     "bfly_decode_enqueue": (i32, [vp, i32, i32]),

@@ -165,6 +165,14 @@ int bfly_prefill(bfly_ctx* ctx, const int32_t* tokens_host, int B, int S, float*
   return guarded(ctx, [&]() -> int { return ctx->engine->prefill(tokens_host, B, S, logits_host, next_tokens_host); });
 }
 
+int bfly_prefill_at(bfly_ctx* ctx, int seq0, const int32_t* tokens_host, int n_seqs, int S, float* logits_host,
+                    int32_t* next_tokens_host) {
+  NEED_CTX(ctx);
+  return guarded(ctx, [&]() -> int {
+    return ctx->engine->prefill_at(seq0, tokens_host, n_seqs, S, logits_host, next_tokens_host);
+  });
+}
+
 int bfly_decode(bfly_ctx* ctx, const int32_t* tokens_host, int B, float* logits_host, int32_t* next_tokens_host) {
   NEED_CTX(ctx);
   return guarded(ctx, [&]() -> int { return ctx->engine->decode(tokens_host, B, logits_host, next_tokens_host); });

@@ -527,7 +527,7 @@ int Engine::check_ready(int B) {
   return BFLY_OK;
 }
 
-int Engine::fetch_outputs(int B, float* logits_host, int32_t* next_host) {
+int Engine::fetch_outputs(int seq0, int B, float* logits_host, int32_t* next_host) {
   const bfly_model_desc& c = d;
   if (logits_host) {
     if (c.tp > 1) {
@@ -536,34 +536,44 @@ int Engine::fetch_outputs(int B, float* logits_host, int32_t* next_host) {
         const int r0 = std::min(c.vocab, r * v_shard), r1 = std::min(c.vocab, (r + 1) * v_shard);
         if (r1 > r0)
           BFLY_CUDA(cudaMemcpy2DAsync(logits_host + r0, (size_t)c.vocab * sizeof(float),
-                                      logits_all + (size_t)r * c.max_batch * v_shard, (size_t)v_shard * sizeof(float),
-                                      (size_t)(r1 - r0) * sizeof(float), B, cudaMemcpyDeviceToHost, stream));
+                                      logits_all + ((size_t)r * c.max_batch + seq0) * v_shard,
+                                      (size_t)v_shard * sizeof(float), (size_t)(r1 - r0) * sizeof(float), B,
+                                      cudaMemcpyDeviceToHost, stream));
       }
     } else {
-      BFLY_CUDA(cudaMemcpy2DAsync(logits_host, (size_t)c.vocab * sizeof(float), logits, (size_t)v_shard * sizeof(float),
-                                  (size_t)c.vocab * sizeof(float), B, cudaMemcpyDeviceToHost, stream));
+      BFLY_CUDA(cudaMemcpy2DAsync(logits_host, (size_t)c.vocab * sizeof(float), logits + (size_t)seq0 * v_shard,
+                                  (size_t)v_shard * sizeof(float), (size_t)c.vocab * sizeof(float), B,
+                                  cudaMemcpyDeviceToHost, stream));
     }
   }
   if (next_host)
-    BFLY_CUDA(cudaMemcpyAsync(next_host, cur_tokens, (size_t)B * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    BFLY_CUDA(cudaMemcpyAsync(next_host, cur_tokens + seq0, (size_t)B * sizeof(int), cudaMemcpyDeviceToHost, stream));
   BFLY_CUDA(cudaStreamSynchronize(stream));
   return BFLY_OK;
 }
 
 int Engine::prefill(const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host) {
+  host_len = 0;
+  return prefill_at(0, tokens_host, B, S, logits_host, next_host);
+}
+
+// Restarts sequences [seq0, seq0 + B) with S tokens each; every other sequence keeps its cache and its
+// length, so prompts of different lengths are loaded group by group and then decoded as one batch.
+int Engine::prefill_at(int seq0, const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host) {
   BFLY_TRY(check_ready(B));
+  BFLY_CHECK(seq0 >= 0 && seq0 + B <= d.max_batch, "prefill: sequences must lie in [0, max_batch)");
   BFLY_CHECK(tokens_host != nullptr && S >= 1 && S <= d.max_ctx && S <= d.max_tokens, "prefill: 1 <= S <= min(max_ctx, max_tokens)");
-  BFLY_CUDA(cudaMemsetAsync(seq_lens, 0, (size_t)B * sizeof(int), stream));
-  host_len = S;
+  BFLY_CUDA(cudaMemsetAsync(seq_lens + seq0, 0, (size_t)B * sizeof(int), stream));
+  host_len = std::max(host_len, S);               // longest sequence: what the KV-overflow checks go by
   const int per_chunk = std::max(1, d.max_tokens / S);
   for (int b0 = 0; b0 < B; b0 += per_chunk) {
     const int nb = std::min(per_chunk, B - b0);
     BFLY_CUDA(cudaMemcpyAsync(tokens_in, tokens_host + (size_t)b0 * S, (size_t)nb * S * sizeof(int),
                               cudaMemcpyHostToDevice, stream));
-    BFLY_TRY(forward(tokens_in, b0, nb, S, logits_host != nullptr, false));
+    BFLY_TRY(forward(tokens_in, seq0 + b0, nb, S, logits_host != nullptr, false));
     // tokens_in is reused by the next chunk: the H2D copy is stream-ordered after this forward
   }
-  return fetch_outputs(B, logits_host, next_host);
+  return fetch_outputs(seq0, B, logits_host, next_host);
 }
 
 int Engine::decode_graph(int B, bool want_logits, GraphEntry** out) {
@@ -600,7 +610,7 @@ int Engine::decode(const int32_t* tokens_host, int B, float* logits_host, int32_
   BFLY_CUDA(cudaMemsetAsync(step_counter, 0, sizeof(int), stream));
   BFLY_CUDA(cudaGraphLaunch(ge->exec, stream));
   g_launch_count += (unsigned long long)ge->kernel_nodes;
-  return fetch_outputs(B, logits_host, next_host);
+  return fetch_outputs(0, B, logits_host, next_host);
 }
 
 int Engine::decode_enqueue(int B, int n_steps) {

@@ -93,6 +93,7 @@ struct Engine {
   int set_page_table(const int32_t* table_host, int n_seqs, int pps);
 
   int prefill(const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);
+  int prefill_at(int seq0, const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);
   int decode(const int32_t* tokens_host, int B, float* logits_host, int32_t* next_host);
   int decode_enqueue(int B, int n_steps);
   int decode_greedy(int B, int n_steps, int32_t* tokens_out_host);
@@ -108,7 +109,7 @@ struct Engine {
   int all_reduce_f32(float* buf, size_t count);
   int all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank);
   int forward(const int* tokens_dev, int seq0, int nb, int S, bool want_logits, bool record_history);
-  int fetch_outputs(int B, float* logits_host, int32_t* next_host);
+  int fetch_outputs(int seq0, int B, float* logits_host, int32_t* next_host);
   int decode_graph(int B, bool want_logits, GraphEntry** out);
 };
 

@@ -128,6 +128,22 @@ class Model:
         self.last_tokens = nxt
         return logits
 
+    def prefill_at(self, seq0: int, tokens: torch.Tensor, want_logits: bool = True) -> Optional[torch.Tensor]:
+        """Ragged batches: restart sequences seq0 .. seq0+n-1 with tokens int32[n,S]; the others keep their cache."""
+        tok = tokens.to(torch.int32).contiguous()
+        n, S = tok.shape
+        logits = torch.empty((n, self.cfg.vocab), dtype=torch.float32) if want_logits else None
+        nxt = torch.empty((n,), dtype=torch.int32)
+        self._check(self.lib.bfly_prefill_at(self.ctx, seq0, tok.data_ptr(), n, S,
+                                             logits.data_ptr() if want_logits else None, nxt.data_ptr()))
+        if self.last_tokens is None or self.last_tokens.numel() < seq0 + n:
+            grown = torch.zeros((seq0 + n,), dtype=torch.int32)
+            if self.last_tokens is not None:
+                grown[:self.last_tokens.numel()] = self.last_tokens
+            self.last_tokens = grown
+        self.last_tokens[seq0:seq0 + n] = nxt
+        return logits
+
     def decode(self, tokens: Optional[torch.Tensor], want_logits: bool = True) -> Optional[torch.Tensor]:
         """tokens int32[B] -> fp32 logits[B,V]; tokens=None continues from the engine's greedy tokens."""
         B = tokens.numel() if tokens is not None else self.last_tokens.numel()

@@ -94,6 +94,13 @@ int bfly_set_page_table(bfly_ctx* ctx, const int32_t* table_host, int n_seqs, in
  * (fp32 [B][vocab], last position, gathered over ranks) and next_tokens_host (int32[B]) may be NULL. */
 int bfly_prefill(bfly_ctx* ctx, const int32_t* tokens_host, int B, int S, float* logits_host,
                  int32_t* next_tokens_host);
+/* Ragged batches: restart only sequences seq0 .. seq0+n_seqs-1 with S tokens each (tokens_host
+ * int32[n_seqs][S]); all other sequences keep their cache and length.  Load prompts of different
+ * lengths group by group, then bfly_decode the whole batch: every kernel reads per-sequence lengths.
+ * Outputs are for the n_seqs sequences of this call.  (No reference counterpart: the reference's
+ * intended "Scheduling System", ref:CLAUDE.md:22, is unimplemented.) */
+int bfly_prefill_at(bfly_ctx* ctx, int seq0, const int32_t* tokens_host, int n_seqs, int S, float* logits_host,
+                    int32_t* next_tokens_host);
 /* One decode step: tokens_host int32[B] (NULL = continue from the engine's own greedy tokens). */
 int bfly_decode(bfly_ctx* ctx, const int32_t* tokens_host, int B, float* logits_host, int32_t* next_tokens_host);
 /* n free-running greedy steps with everything resident on the device (one CUDA graph replay per
