@@ -541,6 +541,76 @@ int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_ex
 }
 
 // ---------------------------------------------------------------------------------------------
+// K9 grouping (prefill): the tokens routed to each LOCAL expert, compacted in token order.  Rows
+// [off[e], off[e] + cnt[e]) of idx / rw belong to local expert e; off[n_local] = rows in total
+// (<= T * min(top_k, n_local)).  One CTA: T * n_local is at most a few 10^4 flags.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) moe_compact_kernel(const float* __restrict__ route_w, int T, int n_local,
+                                                           int* __restrict__ cnt, int* __restrict__ off,
+                                                           int* __restrict__ idx, float* __restrict__ rw) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ int warp_tot[32];
+  __shared__ int base_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+  if (threadIdx.x == 0) base_s = 0;
+  __syncthreads();
+  for (int e = 0; e < n_local; ++e) {
+    const int start = base_s;
+    if (threadIdx.x == 0) off[e] = start;
+    for (int t0 = 0; t0 < T; t0 += blockDim.x) {
+      const int t = t0 + (int)threadIdx.x;
+      const float w = t < T ? route_w[(int64_t)t * n_local + e] : 0.f;
+      const bool on = w > 0.f;
+      const unsigned m = __ballot_sync(0xffffffffu, on);
+      if (lane == 0) warp_tot[warp] = __popc(m);
+      __syncthreads();
+      int before = 0, total = 0;
+      for (int i = 0; i < n_warps; ++i) {
+        const int c = warp_tot[i];
+        if (i < warp) before += c;
+        total += c;
+      }
+      const int base = base_s;
+      if (on) {
+        const int pos = base + before + __popc(m & ((1u << lane) - 1u));
+        idx[pos] = t;
+        rw[pos] = w;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) base_s = base + total;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) cnt[e] = base_s - start;
+  }
+  if (threadIdx.x == 0) off[n_local] = base_s;
+}
+
+// gathers the routed rows of the normed activations into expert order: xg[r] = xn[idx[r]]
+__global__ void moe_gather_kernel(const bf16* __restrict__ xn, const int* __restrict__ idx, const int* __restrict__ off,
+                                  int n_local, bf16* __restrict__ xg, int h) {
+  pdl_trigger();
+  pdl_wait();
+  const int total = off[n_local];
+  for (int r = blockIdx.x; r < total; r += gridDim.x) {
+    const uint4* src = reinterpret_cast<const uint4*>(xn + (int64_t)idx[r] * h);
+    uint4* dst = reinterpret_cast<uint4*>(xg + (int64_t)r * h);
+    for (int i = threadIdx.x; i < h / 8; i += blockDim.x) dst[i] = src[i];
+  }
+}
+
+int launch_moe_group(const float* route_w, const bf16* xn, int T, int h, int n_local, int rows_cap, int* cnt, int* off,
+                     int* idx, float* rw, bf16* xg, cudaStream_t stream) {
+  BFLY_CHECK(T > 0 && h % 8 == 0 && n_local >= 1 && rows_cap >= T, "moe_group: bad shape");
+  BFLY_CUDA(launch_pdl(moe_compact_kernel, dim3(1), dim3(1024), 0, stream, route_w, T, n_local, cnt, off, idx, rw));
+  const int grid = std::min(rows_cap, 148 * 8);
+  BFLY_CUDA(launch_pdl(moe_gather_kernel, dim3(grid), dim3(128), 0, stream, xn, (const int*)idx, (const int*)off, n_local, xg, h));
+  count_launch(2);
+  BFLY_CUDA(cudaGetLastError());
+  return BFLY_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // fold split-K slices into one fp32 buffer (only used in front of an NCCL all-reduce, TP > 1)
 // ---------------------------------------------------------------------------------------------
 __global__ void reduce_partials_kernel(const float* __restrict__ partials, int n_partials, int64_t partial_stride,

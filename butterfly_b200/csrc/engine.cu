@@ -134,6 +134,8 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   {
     const char* env = getenv("BFLY_FUSED_SWIGLU");      // tuning knob; default on
     e->fused_swiglu = !(env && env[0] == '0');
+    env = getenv("BFLY_MOE_GROUPED");                   // tuning knob; default on
+    e->moe_grouped = !(env && env[0] == '0') && e->gated && e->fused_swiglu;
   }
 
   const int h = c.hidden, maxT = c.max_tokens, maxB = c.max_batch;
@@ -180,6 +182,15 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   A(dev_alloc(e, &e->part_ml, pml, wsb));
   if (c.tp > 1) A(dev_alloc(e, &e->red, (size_t)maxT * h, wsb));
   if (c.n_experts) A(dev_alloc(e, &e->route_w, (size_t)maxT * e->experts_local, wsb));
+  if (c.n_experts && e->moe_grouped && maxT >= kMoeGroupedMinTokens) {
+    e->moe_rows_cap = maxT * std::min(c.top_k, e->experts_local);
+    A(dev_alloc(e, &e->moe_cnt, (size_t)e->experts_local, wsb));
+    A(dev_alloc(e, &e->moe_off, (size_t)e->experts_local + 1, wsb));
+    A(dev_alloc(e, &e->moe_idx, (size_t)e->moe_rows_cap, wsb));
+    A(dev_alloc(e, &e->moe_rw, (size_t)e->moe_rows_cap, wsb));
+    A(dev_alloc(e, &e->moe_xg, (size_t)e->moe_rows_cap * h, wsb));
+    A(dev_alloc(e, &e->moe_out, (size_t)maxT * h, wsb));
+  }
   A(dev_alloc(e, &e->logits, (size_t)maxB * e->v_shard, wsb));
   if (c.tp > 1) A(dev_alloc(e, &e->logits_all, (size_t)c.tp * maxB * e->v_shard, wsb));
   A(dev_alloc(e, &e->keys, (size_t)maxB, wsb));
@@ -422,21 +433,58 @@ int Engine::gemm_swiglu(const bf16* W, const bf16* X, int N) {
 }
 
 // Row-parallel output: fold slices and all-reduce when tp > 1; tells the consumer where to read.
-int Engine::row_parallel_finish(int T, int slices, bool allow_fused, const float** src, int* n_partials, bool* fused) {
+int Engine::row_parallel_finish(int T, int slices, bool allow_fused, float* partials, const float** src,
+                                int* n_partials, bool* fused) {
   const int h = d.hidden;
   *fused = false;
-  if (d.tp == 1) { *src = ws; *n_partials = slices; return BFLY_OK; }
+  if (d.tp == 1) { *src = partials; *n_partials = slices; return BFLY_OK; }
   if (allow_fused && p2p_ready && T <= ar.max_rows) {      // decode: the consumer kernel does the all-reduce
-    *src = ws; *n_partials = slices; *fused = true;
+    *src = partials; *n_partials = slices; *fused = true;
     return BFLY_OK;
   }
-  float* buf = ws;
+  float* buf = partials;
   if (slices > 1) {
-    BFLY_TRY(launch_reduce_partials(ws, slices, (int64_t)T * h, red, (int64_t)T * h, stream));
+    BFLY_TRY(launch_reduce_partials(partials, slices, (int64_t)T * h, red, (int64_t)T * h, stream));
     buf = red;
   }
   BFLY_TRY(all_reduce_f32(buf, (size_t)T * h));
   *src = buf; *n_partials = 1;
+  return BFLY_OK;
+}
+
+// MoE prefill: every local expert runs its gate/up (+SwiGLU, x routing weight) and down projections over
+// the tokens routed to it only (top-k of E: 1/4 of the dense work for Mixtral), on rows gathered into
+// expert order; the down projection's epilogue adds each row back into its token's row of moe_out.
+// Row counts stay on the device: the persistent GEMM reads them and skips the tiles beyond.
+int Engine::moe_ffn_grouped(const bf16* w_in, const bf16* w_down, int T) {
+  const int h = d.hidden, f = d.ffn;
+  BFLY_TRY(launch_moe_group(route_w, xn, T, h, experts_local, moe_rows_cap, moe_cnt, moe_off, moe_idx, moe_rw, moe_xg,
+                            stream));
+  BFLY_CUDA(cudaMemsetAsync(moe_out, 0, (size_t)T * h * sizeof(float), stream));
+  for (int e = 0; e < experts_local; ++e) {
+    const GemmPlan pu = gemm_plan(f, T, h, sm_count, kMaxSplits, 1, 1);
+    const GemmPlan pd = gemm_plan(h, T, f, sm_count, kMaxSplits, 0, 1);
+    if (!pu.persistent || !pd.persistent) { set_error("grouped MoE needs persistent GEMM plans (internal)"); return BFLY_ESTATE; }
+    GemmOut ou{};
+    ou.out_bf16 = act;                       // [rows][f] in expert order (the buffer holds max_tokens x E_l x f)
+    ou.ldc = f;
+    ou.n_blocks = 1;
+    ou.f_block = f;
+    ou.route_w = moe_rw;
+    ou.n_rows_dev = moe_cnt + e;
+    ou.row_off_dev = moe_off + e;
+    ou.x_rows = moe_rows_cap;
+    BFLY_TRY(launch_gemm_ex(w_in + (int64_t)e * 2 * f * h, moe_xg, h, pu, ou, stream));
+    GemmOut od{};
+    od.out_f32 = moe_out;
+    od.ldc = h;
+    od.n_rows_dev = moe_cnt + e;
+    od.row_off_dev = moe_off + e;
+    od.row_map = moe_idx;
+    od.x_rows = moe_rows_cap;
+    od.ldw = (int64_t)experts_local * f;
+    BFLY_TRY(launch_gemm_ex(w_down + (int64_t)e * f, act, f, pd, od, stream));
+  }
   return BFLY_OK;
 }
 
@@ -481,7 +529,7 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     else
       BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
     BFLY_TRY(gemm(w.wo, attn_out, q_local * dh, h, T, q_local * dh, &s));
-    BFLY_TRY(row_parallel_finish(T, s, allow_fused, &pend_src, &pend_n, &pend_fused));
+    BFLY_TRY(row_parallel_finish(T, s, allow_fused, ws, &pend_src, &pend_n, &pend_fused));
     any_fused |= pend_fused;
     BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, w.bo, w.ffn_norm_w, w.ffn_norm_b));
     if (c.n_experts)
@@ -489,15 +537,22 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
                                  route_w, stream));
     // Fused SwiGLU epilogue: +5 % at prefill (no fp32 gate/up round trip); at decode the cluster it needs
     // to complete the K sum costs more than the separate activation kernel (measured), so T <= 64 stays unfused.
-    if (gated && fused_swiglu && T > 64) {
-      BFLY_TRY(gemm_swiglu(w.w_in, xn, T));
+    float* ffn_out = ws;
+    if (c.n_experts && moe_out != nullptr && T >= kMoeGroupedMinTokens) {
+      BFLY_TRY(moe_ffn_grouped(w.w_in, w.w_down, T));
+      ffn_out = moe_out;
+      s = 1;
     } else {
-      BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s));
-      BFLY_TRY(launch_act(ws, s, (int64_t)T * ffn_in_rows, w.b_up, gated ? ACT_SWIGLU : ACT_GELU_TANH, n_blocks,
-                          f_block, c.n_experts ? route_w : nullptr, act, T, stream));
+      if (gated && fused_swiglu && T > 64) {
+        BFLY_TRY(gemm_swiglu(w.w_in, xn, T));
+      } else {
+        BFLY_TRY(gemm(w.w_in, xn, h, ffn_in_rows, T, h, &s));
+        BFLY_TRY(launch_act(ws, s, (int64_t)T * ffn_in_rows, w.b_up, gated ? ACT_SWIGLU : ACT_GELU_TANH, n_blocks,
+                            f_block, c.n_experts ? route_w : nullptr, act, T, stream));
+      }
+      BFLY_TRY(gemm(w.w_down, act, ffn_act_cols, h, T, ffn_act_cols, &s));
     }
-    BFLY_TRY(gemm(w.w_down, act, ffn_act_cols, h, T, ffn_act_cols, &s));
-    BFLY_TRY(row_parallel_finish(T, s, allow_fused, &pend_src, &pend_n, &pend_fused));
+    BFLY_TRY(row_parallel_finish(T, s, allow_fused, ffn_out, &pend_src, &pend_n, &pend_fused));
     any_fused |= pend_fused;
     pend_bias = w.b_down;
   }

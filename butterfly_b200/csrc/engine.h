@@ -13,6 +13,7 @@ namespace bfly {
 constexpr int kMaxSplits = 16;           // split-K cap used by the planner inside the engine
 constexpr int kMaxGreedySteps = 4096;    // history rows kept for bfly_decode_greedy
 constexpr size_t kPinnedBytes = 1 << 20;
+constexpr int kMoeGroupedMinTokens = 256;   // MoE forwards of at least this many rows gather tokens per expert
 
 struct NcclId { char bytes[128]; };      // layout of ncclUniqueId
 int nccl_unique_id(void* out128);
@@ -45,6 +46,11 @@ struct Engine {
   int n_blocks = 1, f_block = 0, ffn_in_rows = 0, ffn_act_cols = 0;
   bool gated = true;
   bool fused_swiglu = true;                // gate/up GEMM applies the SwiGLU in its epilogue
+  bool moe_grouped = true;                 // MoE prefill runs each expert over its routed tokens only
+  int moe_rows_cap = 0;                    // max_tokens * min(top_k, experts_local)
+  int *moe_cnt = nullptr, *moe_off = nullptr, *moe_idx = nullptr;
+  float *moe_rw = nullptr, *moe_out = nullptr;
+  bf16* moe_xg = nullptr;
   int v_shard = 0, v0 = 0, v_local = 0;
   int pages_per_seq = 0;
   int64_t n_pages = 0, layer_kv_elems = 0;
@@ -103,7 +109,9 @@ struct Engine {
   int check_ready(int B);
   int gemm(const bf16* W, const bf16* X, int64_t ldx, int M, int N, int K, int* slices_out);
   int gemm_swiglu(const bf16* W, const bf16* X, int N);
-  int row_parallel_finish(int T, int splits, bool allow_fused, const float** src, int* n_partials, bool* fused);
+  int moe_ffn_grouped(const bf16* w_in, const bf16* w_down, int T);
+  int row_parallel_finish(int T, int splits, bool allow_fused, float* partials, const float** src, int* n_partials,
+                          bool* fused);
   int norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,
                  const bf16* beta);
   int all_reduce_f32(float* buf, size_t count);

@@ -318,7 +318,9 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
 
   const int n_groups = (int)gridDim.x >> pair;            // CTAs (or CTA pairs) in the grid
   const int my_group = (int)blockIdx.x >> pair;
-  const int total_units = args.m_units * args.n_tiles;
+  // token rows of this launch: static, or (grouped MoE) read from the device once the producer kernel is done
+  int n_rows = args.N, row_off = 0, n_tiles = args.n_tiles;
+  int total_units = args.m_units * n_tiles;
   const int nkb = (args.K + BK - 1) / BK;
   const uint32_t acc_cols = (uint32_t)bn * (uint32_t)(1 + dual);
 
@@ -329,7 +331,7 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
     // 2D-blocked unit order: bands of kBandUnits weight units; inside a band the weight unit varies fastest,
     // so a wave of ~74 units touches ~8 weight units x ~9 token tiles (both L2-resident) instead of
     // re-streaming every token tile for each weight unit.
-    const int per_band = kBandUnits * args.n_tiles;
+    const int per_band = kBandUnits * n_tiles;
     const int band = u / per_band, rem = u - band * per_band;
     const int band_m = min(kBandUnits, args.m_units - band * kBandUnits);
     const int n_idx = rem / band_m;
@@ -378,6 +380,13 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
   tcgen05_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+  if (args.n_rows_dev != nullptr) {
+    pdl_wait();
+    n_rows = min(args.N, *args.n_rows_dev);
+    row_off = args.row_off_dev != nullptr ? *args.row_off_dev : 0;
+    n_tiles = (n_rows + bn - 1) / bn;
+    total_units = args.m_units * n_tiles;
+  }
 
   if (warp == 0) {
     if (lane == 0) {
@@ -394,7 +403,7 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
       bool waited = false;
       for (int u = my_group; u < total_units; u += n_groups) {
         const Tile t = tile_of(u);
-        const int n_load = t.n0 + (int)cta_rank * (bn >> 1) * pair;
+        const int n_load = row_off + t.n0 + (int)cta_rank * (bn >> 1) * pair;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % stages;
           const uint32_t ph = (uint32_t)(it / stages) & 1u;
@@ -464,7 +473,7 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
       const int feat = t.feat0 + ml;
       const bool row_ok = feat < t.feat_limit;
       for (int c0 = c_begin; c0 < c_end; c0 += 32) {
-        if (t.n0 + c0 >= args.N) break;
+        if (t.n0 + c0 >= n_rows) break;
         uint32_t r[32], ru[32];
         tmem_ld32(taddr + (uint32_t)c0, r);
         if (dual) tmem_ld32(taddr + (uint32_t)(bn + c0), ru);
@@ -472,15 +481,16 @@ __global__ void __launch_bounds__(kPersistThreads) gemm_persistent_kernel(const 
         if (row_ok) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int n = t.n0 + c0 + j;
-            if (n >= args.N) break;
+            if (t.n0 + c0 + j >= n_rows) break;
+            const int n = row_off + t.n0 + c0 + j;
             const float g = __uint_as_float(r[j]);
             if (dual) {
               float y = silu_mul(g, __uint_as_float(ru[j]));
               if (args.route_w != nullptr) y *= args.route_w[(int64_t)n * args.n_blocks + t.blk];
               args.out_bf16[(int64_t)n * args.ldc + feat] = __float2bfloat16_rn(y);
             } else if (args.out_f32 != nullptr) {
-              args.out_f32[(int64_t)n * args.ldc + feat] = g;
+              if (args.row_map != nullptr) args.out_f32[(int64_t)args.row_map[n] * args.ldc + feat] += g;
+              else args.out_f32[(int64_t)n * args.ldc + feat] = g;
             } else {
               args.out_bf16[(int64_t)n * args.ldc + feat] = __float2bfloat16_rn(g);
             }
@@ -563,7 +573,7 @@ int gemm_init() {
 }
 
 // M = output features (dual: gated features, i.e. half the weight rows).
-GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual) {
+GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual, int force_persistent) {
   GemmPlan p{};
   p.M = M; p.N = N; p.K = K;
   p.dual = dual;
@@ -598,6 +608,10 @@ GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual) 
     splits = std::min(splits, kMaxCluster);
     p.cluster = 1;
   }
+  if (force_persistent && N >= 128) {        // grouped MoE: the row count lives on the device, only the persistent
+    splits = 1;                              // kernel can follow it
+    p.cluster = 0;
+  }
   p.splits = splits;
   // Tensor-bound regime (>= 128 tokens per tile, no split): pair adjacent weight tiles with cta_group::2 so
   // each SM reads only half of the token tile from shared memory (a single CTA's 128x256 UMMA needs
@@ -608,7 +622,7 @@ GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual) 
   // token tiles of 256 (plain) / 128 (fused SwiGLU).  BFLY_GEMM_PERSISTENT=0 disables.
   static const bool allow_persist = [] { const char* e = getenv("BFLY_GEMM_PERSISTENT"); return !(e && e[0] == '0'); }();
   p.persistent = 0;
-  if (allow_persist && splits == 1 && !p.cluster && N >= 128) {
+  if ((allow_persist || force_persistent) && splits == 1 && !p.cluster && N >= 128) {
     p.persistent = 1;
     p.bn = dual ? 128 : std::min(256, ((N + 63) / 64) * 64);
     p.pair = (allow_pair && m_tiles >= 2) ? 1 : 0;
@@ -654,8 +668,14 @@ int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& pl
              "gemm: cluster reduction buffer does not fit the operand ring");
   CUtensorMap mw, mx;
   const int64_t w_rows = dual ? 2 * (int64_t)plan.M : plan.M;
-  BFLY_TRY(make_map(&mw, W, w_rows, plan.K, plan.K, BM));
-  BFLY_TRY(make_map(&mx, X, plan.N, plan.K, ldx, plan.bn >> pair));
+  const bool grouped = out.n_rows_dev != nullptr;
+  BFLY_CHECK(!grouped || plan.persistent, "gemm: device-side row counts need the persistent kernel");
+  BFLY_CHECK(grouped || (out.row_off_dev == nullptr && out.row_map == nullptr), "gemm: row_off / row_map need n_rows_dev");
+  BFLY_CHECK(out.row_map == nullptr || (out.out_f32 != nullptr && !dual), "gemm: row_map needs the fp32 output");
+  BFLY_CHECK(out.ldw == 0 || (out.ldw >= plan.K && out.ldw % 8 == 0), "gemm: ldw >= K and ldw % 8 == 0");
+  BFLY_CHECK(out.x_rows == 0 || out.x_rows >= plan.N, "gemm: x_rows >= N");
+  BFLY_TRY(make_map(&mw, W, w_rows, plan.K, out.ldw ? out.ldw : plan.K, BM));
+  BFLY_TRY(make_map(&mx, X, out.x_rows ? out.x_rows : plan.N, plan.K, ldx, plan.bn >> pair));
   GemmArgs a{};
   a.M = plan.M; a.N = plan.N; a.K = plan.K;
   a.bn = plan.bn; a.stages = plan.stages; a.splits = plan.splits;
@@ -673,6 +693,7 @@ int launch_gemm_ex(const bf16* W, const bf16* X, int64_t ldx, const GemmPlan& pl
   while ((int)cols < plan.bn * (1 + dual) * (plan.persistent ? 2 : 1)) cols <<= 1;
   a.tmem_cols = cols;
   a.out_f32 = out.out_f32; a.out_bf16 = out.out_bf16; a.route_w = out.route_w;
+  a.n_rows_dev = out.n_rows_dev; a.row_off_dev = out.row_off_dev; a.row_map = out.row_map;
   a.split_stride = out.split_stride; a.ldc = out.ldc;
   int m_tiles = ceil_div(plan.M, BM);
   if (dual) m_tiles = out.n_blocks * ceil_div(out.f_block, BM);

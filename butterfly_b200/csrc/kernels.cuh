@@ -61,6 +61,10 @@ int launch_lm_finalize(const float* partials, int n_partials, int64_t partial_st
 int launch_pick_tokens_pitched(const unsigned long long* keys, int n_ranks, int pitch, int T, int* tokens_out,
                                cudaStream_t stream);
 int launch_advance(int* seq_lens, int B, int S, int* step_counter, unsigned* ar_step, cudaStream_t stream);
+// routed-token grouping for MoE prefill: per local expert e, rows [off[e], off[e]+cnt[e]) of idx (token id), rw
+// (routing weight) and xg (gathered activations); off has n_local + 1 entries
+int launch_moe_group(const float* route_w, const bf16* xn, int T, int h, int n_local, int rows_cap, int* cnt, int* off,
+                     int* idx, float* rw, bf16* xg, cudaStream_t stream);
 int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_experts, int top_k,
                       int first_local, int n_local, float* route_w, cudaStream_t stream);
 int launch_reduce_partials(const float* partials, int n_partials, int64_t partial_stride, float* out,
@@ -107,9 +111,16 @@ struct GemmOut {
   int64_t ldc;
   int n_blocks, f_block;    // dual only
   const float* route_w;     // dual + MoE: [N][n_blocks], nullptr otherwise
+  // Grouped MoE prefill (persistent plans only): this launch handles the token rows
+  // [*row_off_dev, *row_off_dev + min(N, *n_rows_dev)) of X -- counts that only exist on the device.
+  const int* n_rows_dev;    // nullptr: all N rows, starting at row 0
+  const int* row_off_dev;
+  const int* row_map;       // fp32 output: row r of X accumulates (+=) into output row row_map[r]
+  int64_t x_rows;           // rows X really has (TMA bound); 0 = N
+  int64_t ldw;              // row pitch of W in elements; 0 = K
 };
 int gemm_init();        // resolves cuTensorMapEncodeTiled, sets kernel attributes (once per process)
-GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual = 0);
+GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual = 0, int force_persistent = 0);
 // number of fp32 slices a consumer must fold for this plan
 inline int gemm_slices(const GemmPlan& p) { return (p.cluster || p.splits == 1) ? 1 : p.splits; }
 // ldx = row pitch of X in elements (>= K, multiple of 8).

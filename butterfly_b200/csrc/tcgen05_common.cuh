@@ -137,6 +137,9 @@ struct GemmArgs {
   float* out_f32;
   bf16* out_bf16;
   const float* route_w;        // dual + MoE: [N][n_blocks] routing weights (0 = not routed), else nullptr
+  const int* n_rows_dev;       // persistent kernel, grouped MoE: device-side row count / first row / output row map
+  const int* row_off_dev;
+  const int* row_map;
   int64_t split_stride;
   int64_t ldc;
 };

@@ -126,6 +126,15 @@ def test_mixtral_8x7b_width_shallow_parity(cuda):
     _run_parity(MIXTRAL_8X7B.with_layers(1), B=3, S=20, n_steps=2, device_synth=True)
 
 
+def test_mixtral_grouped_prefill_parity(cuda):
+    """Forwards of >= 256 rows run every expert over its routed tokens only (device-side compaction, gathered
+    rows, persistent GEMMs that read the row counts on the device, scatter-add epilogue): tiny shape with 8
+    local experts, then the real Mixtral width (the dense-path tests above stay below 256 rows)."""
+    _run_parity(tiny("mixtral"), B=3, S=100, n_steps=2, device_synth=True)
+    _run_parity(tiny("mixtral", n_experts=2), B=2, S=150, n_steps=1, device_synth=True)
+    _run_parity(MIXTRAL_8X7B.with_layers(1), B=2, S=160, n_steps=1, device_synth=True)
+
+
 @pytest.mark.parametrize("B,S,max_tokens", [(1, 1, None), (2, 33, None), (5, 31, 64), (3, 97, 128), (1, 200, None)])
 def test_prefill_edge_shapes_and_chunking(cuda, B, S, max_tokens):
     """Ragged / minimal shapes: one-token prompts, prompts that are not a multiple of the 32-token tile or page,
