@@ -68,6 +68,11 @@ def test_tp2_tiny(cuda, family, tmp_path):
     _run(tiny(family), 2, B=3, S=10, steps=4, tmp_path=tmp_path)
 
 
+def test_tp2_mixtral_grouped_prefill(cuda, tmp_path):
+    """A 300-row prefill takes the grouped expert path (4 local experts per rank), its output all-reduced by NCCL."""
+    _run(tiny("mixtral"), 2, B=2, S=150, steps=2, tmp_path=tmp_path)
+
+
 def test_tp2_llama3_8b_width(cuda, tmp_path):
     _run(LLAMA3_8B.with_layers(2), 2, B=4, S=40, steps=3, tmp_path=tmp_path)
 
