@@ -1,0 +1,44 @@
+"""Host mirror of the paged KV layout (butterfly_b200/kv_layout.py) against the offset formulas the kernels use
+(csrc/kernels.cuh: kv_k_offset / kv_v_offset, restated here in plain Python) -- CPU only."""
+import pytest
+import torch
+
+from butterfly_b200.kv_layout import pack_pages, unpack_pages
+
+
+def k_offset(slot, dd, d):
+    chunk = dd >> 3
+    if d >= 64:
+        chunk ^= (slot & 1) << 2
+    return slot * d + (chunk << 3) + (dd & 7)
+
+
+def v_offset(slot, dd, d):
+    return (slot >> 5) * d * 32 + dd * 32 + (slot & 31)
+
+
+@pytest.mark.parametrize("d", [32, 64, 128])
+@pytest.mark.parametrize("ps", [32, 64])
+def test_pack_matches_the_device_offsets_and_round_trips(d, ps):
+    g = torch.Generator().manual_seed(d * 1000 + ps)
+    n_pages, kvh = 3, 2
+    k = torch.randn((n_pages, kvh, ps, d), generator=g)
+    v = torch.randn((n_pages, kvh, ps, d), generator=g)
+    pages = pack_pages(k, v)
+    assert pages.shape == (n_pages, 2, kvh, ps * d)
+    for page in range(n_pages):
+        for head in range(kvh):
+            for slot in range(ps):
+                for dd in range(0, d, 5):
+                    assert pages[page, 0, head, k_offset(slot, dd, d)] == k[page, head, slot, dd]
+                    assert pages[page, 1, head, v_offset(slot, dd, d)] == v[page, head, slot, dd]
+    k2, v2 = unpack_pages(pages, ps, d)
+    assert torch.equal(k2, k) and torch.equal(v2, v)
+
+
+@pytest.mark.parametrize("d", [32, 64, 128])
+def test_offsets_are_a_bijection_inside_a_block(d):
+    ps = 64
+    ks = {k_offset(s, x, d) for s in range(ps) for x in range(d)}
+    vs = {v_offset(s, x, d) for s in range(ps) for x in range(d)}
+    assert ks == set(range(ps * d)) and vs == set(range(ps * d))
