@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <utility>
@@ -62,8 +63,12 @@ struct PerDeviceOnce {
 };
 
 // Counts kernel launches made by this library (bench.py reports it as gpu_launches).
-extern unsigned long long g_launch_count;
-inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
+extern std::atomic<unsigned long long> g_launch_count;
+extern thread_local unsigned long long t_launch_count;      // this thread's share (graph-capture accounting)
+inline void count_launch(int n = 1) {
+  g_launch_count.fetch_add((unsigned long long)n, std::memory_order_relaxed);
+  t_launch_count += (unsigned long long)n;
+}
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -17,7 +17,8 @@
 
 namespace bfly {
 
-unsigned long long g_launch_count = 0;
+std::atomic<unsigned long long> g_launch_count{0};
+thread_local unsigned long long t_launch_count = 0;
 
 // ---- NCCL, resolved at run time so the library loads (and exports its ABI) without NCCL/GPU ----
 namespace {
@@ -636,13 +637,13 @@ int Engine::decode_graph(int B, bool want_logits, GraphEntry** out) {
   auto it = graphs.find(key);
   if (it != graphs.end()) { *out = &it->second; return BFLY_OK; }
   GraphEntry ge{};
-  const unsigned long long before = g_launch_count;
+  const unsigned long long before = t_launch_count;
   cudaGraph_t graph = nullptr;
   BFLY_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
   const int rc = forward(cur_tokens, 0, B, 1, want_logits, true);
   const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
-  ge.kernel_nodes = (int)(g_launch_count - before);
-  g_launch_count = before;                      // captured launches did not execute
+  ge.kernel_nodes = (int)(t_launch_count - before);
+  g_launch_count.fetch_sub((unsigned long long)ge.kernel_nodes, std::memory_order_relaxed);   // captured, not executed
   if (rc != BFLY_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
   BFLY_CUDA(ce);
   const cudaError_t ie = cudaGraphInstantiate(&ge.exec, graph, 0);
