@@ -21,6 +21,12 @@ def test_header_and_ctypes_table_agree():
     assert hdr == set(_lib.SIGNATURES), (hdr ^ set(_lib.SIGNATURES))
 
 
+def test_integration_notes_name_every_entry_point():
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = sorted(s for s in header_symbols() if s not in doc)
+    assert not missing, f"INTEGRATION.md does not mention {missing}"
+
+
 def test_library_loads_and_exports_every_symbol():
     lib = _lib.load()
     for name in header_symbols():
