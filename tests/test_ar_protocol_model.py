@@ -78,7 +78,8 @@ def cta_program(world, me, call, row, two_shot, result, n_par=2):
 def rank_program(world, me, n_calls, rows, two_shot, result, rng, n_par=2):
     """All calls of one rank: the CTAs of a call run interleaved; the next call starts when all are done."""
     for call in range(n_calls):
-        ctas = [cta_program(world, me, call, row, two_shot, result, n_par) for row in range(rows)]
+        mode = two_shot(call) if callable(two_shot) else two_shot
+        ctas = [cta_program(world, me, call, row, mode, result, n_par) for row in range(rows)]
         while ctas:
             g = rng.choice(ctas)
             try:
@@ -109,6 +110,24 @@ def test_random_interleavings_never_overwrite_or_read_stale(tp, rows, two_shot):
             steps += 1
             assert steps < 2_000_000, "protocol dead-locked"
         assert len(result) == tp * n_calls * rows
+
+
+def test_modes_may_alternate_from_call_to_call():
+    """The mode depends on the batch size, so consecutive calls may differ; they share slots and flags."""
+    tp, rows, n_calls = 4, 5, 9
+    for pattern in (lambda c: c % 2 == 0, lambda c: c % 3 == 0, lambda c: c in (1, 2, 5)):
+        for seed in range(8):
+            rng = random.Random(seed)
+            world = [Rank(r, tp, rows) for r in range(tp)]
+            result = {}
+            progs = {r: rank_program(world, r, n_calls, rows, pattern, result, rng) for r in range(tp)}
+            while progs:
+                r = rng.choice(list(progs))
+                try:
+                    next(progs[r])
+                except StopIteration:
+                    del progs[r]
+            assert len(result) == tp * n_calls * rows
 
 
 def test_a_rank_is_never_more_than_one_call_ahead():
