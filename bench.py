@@ -193,6 +193,48 @@ def measure_dominant_gemm(lib, M, N, K, iters=20):
             "ms": ms, "algo_bytes": algo_bytes, "gbs": algo_bytes / ms / 1e6}
 
 
+def measure_decode_attention(lib, batch, ctx, nq, nk, d, max_ctx, iters=12):
+    """Live roofline of the second-largest kernel: paged decode attention of one layer (K and V of every
+    cached token read once).  Same split rule as the engine (csrc/attn_decode.cu: attn_decode_splits)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    ps = 32
+    pps = (ctx + ps - 1) // ps
+    n_pages = batch * pps
+    n_buf = 3                                            # rotate caches so no launch re-reads L2-resident data
+    pages = [torch.randn((n_pages, 2, nk, ps * d), device=dev, dtype=torch.float32).to(torch.bfloat16)
+             for _ in range(n_buf)]
+    table = torch.arange(n_pages, dtype=torch.int32, device=dev).reshape(batch, pps)
+    q = torch.randn((batch, nq * d), device=dev, dtype=torch.float32).to(torch.bfloat16)
+    lens = torch.full((batch,), ctx - 1, dtype=torch.int32, device=dev)
+    out = torch.empty((batch, nq * d), device=dev, dtype=torch.bfloat16)
+    n_splits, tiles = 1, max(1, (max_ctx + 31) // 32)
+    while batch * nk * n_splits < 96 and n_splits < 32 and tiles // (n_splits + 1) >= 8:
+        n_splits += 1
+    part_o = torch.empty((batch * nq * n_splits * d,), device=dev, dtype=torch.float32)
+    part_ml = torch.empty((batch * nq * n_splits * 2,), device=dev, dtype=torch.float32)
+    st = torch.cuda.current_stream()
+
+    def launch(i):
+        rc = lib.bfly_k_attn_decode(q.data_ptr(), pages[i % n_buf].data_ptr(), table.data_ptr(), pps, ps, nk, d,
+                                    lens.data_ptr(), 1, batch, nq, part_o.data_ptr(), part_ml.data_ptr(), n_splits,
+                                    out.data_ptr(), st.cuda_stream)
+        assert rc == 0, lib.bfly_last_error(None)
+
+    for i in range(3):
+        launch(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for i in range(iters):
+        launch(i)
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    algo_bytes = batch * ctx * nk * d * 2 * 2
+    return {"kernel": "attn_decode_kernel (+ attn_combine_kernel when split)", "n_splits": n_splits, "kernel_ms": ms,
+            "algo_bytes_per_launch": algo_bytes, "achieved": algo_bytes / ms / 1e6, "unit": "GB/s", "bound": "hbm"}
+
+
 def run_gpu(args):
     from butterfly_b200 import LLAMA3_8B, Model, SyntheticSource, _lib, make_plan, synthetic_tokens
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -310,6 +352,12 @@ def run_gpu(args):
             "prefill": {"tokens_per_s": BATCH * CTX / (prefill_ms / 1e3), "ms": prefill_ms, "tokens": BATCH * CTX},
             "setup_s": setup_s,
         }
+        try:                                             # second-largest kernel; never allowed to cost the line
+            attn = measure_decode_attention(lib, BATCH, CTX, plan.q_local, plan.kv_local, cfg.head_dim, model.max_ctx)
+            attn["peak"], attn["frac"] = hbm_peak, attn["achieved"] / hbm_peak
+            line["roofline_attention"] = attn
+        except Exception as exc:                         # noqa: BLE001
+            line["roofline_attention"] = {"error": str(exc)[:200]}
         if args.shard_of > 1:
             line["INVALID"] = (f"profiling run: rank 0's shard of a tp={tp} plan on one GPU with the collectives "
                                "skipped; per-rank compute time only, results are not a model output")
