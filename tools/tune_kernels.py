@@ -1,8 +1,9 @@
 #!/usr/bin/env python
 """Micro-benchmarks of the decode-step kernels on one B200, through the C ABI (run under gpurun).
 
-    python tools/tune_kernels.py gemm     # split-K / stage sweep for the Llama-3-8B decode GEMM shapes
-    python tools/tune_kernels.py attn     # context-split sweep for paged decode attention
+    python tools/tune_kernels.py gemm [tp] [model]   # split-K / stage sweep for the decode GEMM shapes of one rank
+    python tools/tune_kernels.py attn [tp] [model]   # context-split sweep for paged decode attention
+(model: llama3-8b (default, B=32 ctx 2048) or llama3-70b (B=64 ctx 4096))
 
 Weights / KV buffers are rotated so that no launch re-reads L2-resident data; times are CUDA-event
 averages over the rotation.  Prints GB/s of algorithmic bytes against MEASURED_PEAKS.json.
@@ -40,9 +41,15 @@ def time_launches(fn, n, warm=3):
     return e0.elapsed_time(e1) / n
 
 
-def tune_gemm(tp=1, batch=32):
+SHAPES = {  # h, f, nq, nk, d, V, batch, ctx
+    "llama3-8b": (4096, 14336, 32, 8, 128, 128256, 32, 2048),
+    "llama3-70b": (8192, 28672, 64, 8, 128, 128256, 64, 4096),
+}
+
+
+def tune_gemm(tp=1, model="llama3-8b"):
     lib = _lib.load()
-    h, f, nq, nk, d, V = 4096, 14336, 32, 8, 128, 128256
+    h, f, nq, nk, d, V, batch, _ = SHAPES[model]
     shapes = {"qkv": ((nq + 2 * nk) * d // tp, h), "wo": (h, nq * d // tp), "gate_up": (2 * f // tp, h),
               "down": (h, f // tp), "lm_head": (V // tp, h)}
     N = batch
@@ -98,9 +105,10 @@ def tune_swiglu(tp=1, batch=32):
         print(f"  splits={splits} (0=planner): {ms * 1e3:6.1f} us  {2 * f * h * 2 / ms / 1e6 / pk * 100:4.0f}%")
 
 
-def tune_attn(tp=1, batch=32, ctx=2048):
+def tune_attn(tp=1, model="llama3-8b"):
     lib = _lib.load()
-    nq, nk, d, ps = 32 // tp, 8 // tp, 128, 32
+    _, _, nq_all, nk_all, d, _, batch, ctx = SHAPES[model]
+    nq, nk, ps = nq_all // tp, nk_all // tp, 32
     pps = (ctx + ps - 1) // ps
     n_pages = batch * pps
     n_buf = 3
@@ -129,12 +137,13 @@ def tune_attn(tp=1, batch=32, ctx=2048):
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "gemm"
     tp = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    model = sys.argv[3] if len(sys.argv) > 3 else "llama3-8b"
     if what == "gemm":
-        tune_gemm(tp)
+        tune_gemm(tp, model)
     elif what == "attn":
-        tune_attn(tp)
+        tune_attn(tp, model)
     elif what == "swiglu":
         tune_swiglu(tp)
     else:
-        tune_gemm(tp)
-        tune_attn(tp)
+        tune_gemm(tp, model)
+        tune_attn(tp, model)
