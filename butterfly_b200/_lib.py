@@ -46,6 +46,7 @@ SIGNATURES = {
     "bfly_comm_unique_id": (i32, [vp]),
     "bfly_comm_init": (i32, [vp, vp, i32, i32]),
     "bfly_set_page_table": (i32, [vp, vp, i32, i32]),
+    "bfly_set_ar_mode": (i32, [vp, i32]),
     "bfly_prefill": (i32, [vp, vp, i32, i32, vp, vp]),
     "bfly_prefill_at": (i32, [vp, i32, vp, i32, i32, vp, vp]),
     "bfly_decode": (i32, [vp, vp, i32, vp, vp]),
@@ -58,6 +59,7 @@ SIGNATURES = {
     "bfly_k_add_norm": (i32, [vp, vp, i32, i64, vp, vp, vp, f32, i32, vp, i32, i32, vp]),
     "bfly_k_rope_kv": (i32, [vp, i32, i64, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp]),
     "bfly_k_attn_decode": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, i32, vp, vp, i32, vp, vp]),
+    "bfly_k_attn_decode_splits": (i32, [i32, i32, i32]),
     "bfly_k_attn_prefill": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, i32, vp, vp]),
     "bfly_k_attn_decode_static": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, i32, i32, vp, vp]),
     "bfly_k_act": (i32, [vp, i32, i64, vp, i32, i32, i32, vp, vp, i32, vp]),

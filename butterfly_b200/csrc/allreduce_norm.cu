@@ -38,10 +38,18 @@ __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
 }
 
 // spin until a peer has published this call's epoch; a lost peer must not hang the GPU
+// (60 s of wall clock: ranks may legitimately be seconds apart, e.g. while one of them instantiates a graph)
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void wait_epoch(const unsigned* f, unsigned epoch) {
-  const long long t0 = clock64();
+  if (ld_acquire_sys_u32(f) == epoch) return;
+  const unsigned long long t0 = globaltimer_ns();
+  unsigned spins = 0;
   while (ld_acquire_sys_u32(f) != epoch) {
-    if (clock64() - t0 > 8000000000ll) __trap();
+    if ((++spins & 1023u) == 0u && globaltimer_ns() - t0 > 60000000000ull) __trap();
   }
 }
 
@@ -188,7 +196,7 @@ __global__ void __launch_bounds__(1024) ar_add_norm_kernel(
 int launch_ar_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
                        const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
                        int T, int h, const ArPeers& peers, int call_idx, const unsigned* step_ptr, int calls_per_step,
-                       cudaStream_t stream) {
+                       int two_shot, cudaStream_t stream) {
   BFLY_CHECK(T > 0 && T <= peers.max_rows && h % 4 == 0 && h * 4 <= 160 * 1024, "ar_add_norm: bad shape");
   BFLY_CHECK(n_partials >= 1 && partials != nullptr && peers.tp >= 2 && peers.tp <= kMaxPeers, "ar_add_norm: bad peers");
   const size_t smem = (size_t)h * sizeof(float);
@@ -198,9 +206,6 @@ int launch_ar_add_norm(float* residual, const float* partials, int n_partials, i
     return (int)BFLY_OK;
   }));
   const int threads = std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
-  // every rank takes the same branch: T, h and tp are identical across the group (and so must the knob be)
-  static const int forced = [] { const char* e = getenv("BFLY_AR_TWO_SHOT"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
-  const int two_shot = forced >= 0 ? forced : (peers.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
   BFLY_CUDA(launch_pdl(ar_add_norm_kernel, dim3(T), dim3(threads), smem, stream, residual, partials, n_partials,
                        partial_stride, bias, gamma, beta, eps, layer_norm, out, h, peers, call_idx, step_ptr,
                        calls_per_step, two_shot));

@@ -159,6 +159,11 @@ int bfly_set_page_table(bfly_ctx* ctx, const int32_t* table_host, int n_seqs, in
   });
 }
 
+int bfly_set_ar_mode(bfly_ctx* ctx, int mode) {
+  NEED_CTX(ctx);
+  return guarded(ctx, [&]() -> int { return ctx->engine->set_ar_mode(mode); });
+}
+
 int bfly_prefill(bfly_ctx* ctx, const int32_t* tokens_host, int B, int S, float* logits_host,
                  int32_t* next_tokens_host) {
   NEED_CTX(ctx);
@@ -244,6 +249,18 @@ int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int3
     return launch_attn_decode(cb(q_bf16), kv, seq_lens, S, T, nq, part_o, part_ml, n_splits, mb(out_bf16),
                               as_stream(stream));
   });
+}
+
+int bfly_k_attn_decode_splits(int T, int kv_local, int max_ctx) {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) sms = v;
+  } else {
+    cudaGetLastError();
+  }
+  if (T < 1 || kv_local < 1 || max_ctx < 1) return 0;
+  return attn_decode_splits(T, kv_local, max_ctx, sms);
 }
 
 int bfly_k_attn_prefill(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,

@@ -95,15 +95,17 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
     bulk_copy_g2s(dst + kBlockBytes, vp, kBlockBytes, bar);
   };
   {
-    const int last_tile = n_tiles - 1;                 // holds this step's freshly appended K/V
+    // S == 1: only the last tile holds K/V appended by the predecessor kernel.  S > 1: the S new tokens of a
+    // sequence may sit in earlier tiles too, so nothing is fetched ahead of the dependency.
+    const int last_tile = n_tiles - 1;
     const int n_pre = min(kStages, my_tiles);
-    if (lane == 0)
+    if (lane == 0 && S == 1)
       for (int i = 0; i < n_pre; ++i)
         if (tile_begin + warp + i * kWarps != last_tile) issue(i);
-    pdl_wait();                                        // q and the new K/V row are ready from here on
+    pdl_wait();                                        // q and the new K/V rows are ready from here on
     if (lane == 0)
       for (int i = 0; i < n_pre; ++i)
-        if (tile_begin + warp + i * kWarps == last_tile) issue(i);
+        if (S != 1 || tile_begin + warp + i * kWarps == last_tile) issue(i);
   }
 
   // Q as B fragments: head r (< G), the same d-permutation as the K chunks (chunk c of every 64 bytes)

@@ -137,6 +137,8 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     e->fused_swiglu = !(env && env[0] == '0');
     env = getenv("BFLY_MOE_GROUPED");                   // tuning knob; default on
     e->moe_grouped = !(env && env[0] == '0') && e->gated && e->fused_swiglu;
+    env = getenv("BFLY_AR_TWO_SHOT");                   // initial all-reduce mode; bfly_set_ar_mode() changes it
+    e->ar_mode = env ? (env[0] == '1' ? 1 : 0) : -1;
   }
 
   const int h = c.hidden, maxT = c.max_tokens, maxB = c.max_batch;
@@ -146,25 +148,22 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   size_t ws = 0;
   for (int g = 0; g < 5; ++g) {
     const int n_cap = (g == 4) ? maxB : maxT;
-    for (int n = 1; n <= n_cap; n = (n < 16 ? n + 1 : n + 16)) {
+    for (int n = 1; n <= n_cap; ++n) {          // every row count: the planner is not monotone in n
       const GemmPlan p = gemm_plan(gemm_m[g], n, gemm_k[g], e->sm_count, kMaxSplits);
       ws = std::max(ws, (size_t)p.splits * n * gemm_m[g]);
     }
-    const GemmPlan p = gemm_plan(gemm_m[g], n_cap, gemm_k[g], e->sm_count, kMaxSplits);
-    ws = std::max(ws, (size_t)p.splits * n_cap * gemm_m[g]);
   }
   e->ws_elems = ws + 64;
+  // split-context attention scratch: attn_decode_splits() is not monotone in T, so take the maximum over
+  // EVERY row count a forward can see (forward() checks the request against these capacities)
   size_t po = 0, pml = 0;
-  for (int t = 1; t <= maxT; t = (t < 64 ? t + 1 : t + 64)) {
+  for (int t = 1; t <= maxT; ++t) {
     const int s = attn_decode_splits(t, e->kv_local, c.max_ctx, e->sm_count);
     po = std::max(po, (size_t)t * e->q_local * s * c.head_dim);
     pml = std::max(pml, (size_t)t * e->q_local * s * 2);
   }
-  {
-    const int s = attn_decode_splits(maxT, e->kv_local, c.max_ctx, e->sm_count);
-    po = std::max(po, (size_t)maxT * e->q_local * s * c.head_dim);
-    pml = std::max(pml, (size_t)maxT * e->q_local * s * 2);
-  }
+  e->part_o_elems = po;
+  e->part_ml_elems = pml;
 
   int rc = BFLY_OK;
   uint64_t* wsb = &e->workspace_bytes;
@@ -496,8 +495,10 @@ int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call,
   const int ln = d.family == BFLY_FAMILY_GPT2;
   if (fused) {
     const int idx = (*ar_call)++;
+    // every rank takes the same branch: T, h, tp and the mode are identical across the group
+    const int two_shot = ar_mode >= 0 ? ar_mode : (d.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
     return launch_ar_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, ar, idx,
-                              ar_step, 2 * d.n_layers, stream);
+                              ar_step, 2 * d.n_layers, two_shot, stream);
   }
   return launch_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, stream);
 }
@@ -527,8 +528,13 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
                             stream));
     if (S > 1)
       BFLY_TRY(launch_attn_prefill(q, kv, lens, S, nb, q_local, attn_out, stream));
-    else
+    else {
+      if ((size_t)T * q_local * attn_splits * dh > part_o_elems || (size_t)T * q_local * attn_splits * 2 > part_ml_elems) {
+        set_error("split-attention scratch too small (internal sizing error)");
+        return BFLY_ESTATE;
+      }
       BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
+    }
     BFLY_TRY(gemm(w.wo, attn_out, q_local * dh, h, T, q_local * dh, &s));
     BFLY_TRY(row_parallel_finish(T, s, allow_fused, ws, &pend_src, &pend_n, &pend_fused));
     any_fused |= pend_fused;
@@ -694,6 +700,21 @@ int Engine::decode_greedy(int B, int n_steps, int32_t* tokens_out_host) {
   } else {
     BFLY_CUDA(cudaStreamSynchronize(stream));
   }
+  return BFLY_OK;
+}
+
+// Mode of the fused decode all-reduce: -1 = by size (two-shot for rows >= 1 MiB at tp >= 4), 0 = one-shot,
+// 1 = two-shot.  Must be set identically on every rank.  Captured decode graphs embed the mode: drop them.
+int Engine::set_ar_mode(int mode) {
+  BFLY_CHECK(mode >= -1 && mode <= 1, "set_ar_mode: mode in {-1, 0, 1}");
+  BFLY_CUDA(cudaSetDevice(device));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  if (mode != ar_mode) {
+    for (auto& kv : graphs)
+      if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    graphs.clear();
+  }
+  ar_mode = mode;
   return BFLY_OK;
 }
 

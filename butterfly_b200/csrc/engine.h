@@ -71,7 +71,7 @@ struct Engine {
   float *logits = nullptr, *logits_all = nullptr;
   unsigned long long *keys = nullptr, *keys_all = nullptr;
   int *tokens_in = nullptr, *cur_tokens = nullptr, *history = nullptr;
-  size_t ws_elems = 0;
+  size_t ws_elems = 0, part_o_elems = 0, part_ml_elems = 0;   // scratch capacities, in elements
   void* pinned = nullptr;
   std::vector<void*> allocations;
   uint64_t weight_bytes = 0, kv_bytes = 0, workspace_bytes = 0;
@@ -81,6 +81,7 @@ struct Engine {
   ArPeers ar{};
   bool p2p_ready = false;
   unsigned* ar_step = nullptr;
+  int ar_mode = -1;                       // -1 by size, 0 one-shot, 1 two-shot (set_ar_mode)
   std::vector<void*> ipc_opened;
   int p2p_init();
   std::map<int, GraphEntry> graphs;       // key = B*2 + want_logits
@@ -97,6 +98,7 @@ struct Engine {
   int weights_ready();
   int comm_init(const void* id128, int world, int rank);
   int set_page_table(const int32_t* table_host, int n_seqs, int pps);
+  int set_ar_mode(int mode);
 
   int prefill(const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);
   int prefill_at(int seq0, const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);

@@ -80,7 +80,7 @@ struct ArPeers {
 int launch_ar_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
                        const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
                        int T, int h, const ArPeers& peers, int call_idx, const unsigned* step_ptr, int calls_per_step,
-                       cudaStream_t stream);
+                       int two_shot, cudaStream_t stream);
 
 // attn_decode.cu -- paged-KV attention, one query token per (virtual) sequence, split over the context
 int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count);

@@ -10,19 +10,26 @@
 // scratch lives here, in a fixed array that is part of the loaded library image.
 //
 // What to know before using it:
-//   * The array is kStaticScratchBytes (4 MiB) on EVERY GPU that loads this library, from load until
-//     the process exits, whether or not this entry point is ever called.
-//   * A request needs T * nq * n_splits * (head_dim + 2) floats.  Larger requests are refused with
-//     BFLY_EINVAL and a message that states both numbers; nothing is launched in that case.
+//   * The array is kStaticScratchBytes (4 MiB) per GPU and belongs to the library's device code, not to
+//     any allocator.  CUDA loads device code lazily by default, so the 4 MiB are claimed on a GPU when
+//     this entry point first runs there (the address lookup below loads the module that holds the
+//     array); from then on they stay until the process exits.  Setting CUDA_MODULE_LOADING=EAGER moves
+//     that moment to library load.  Either way the FIRST call on a device needs 4 MiB of free device
+//     memory: make it during start-up, before your pool takes the rest of the GPU.  If the memory is not
+//     there, that call returns BFLY_ECUDA with the runtime's message and launches nothing.
+//   * A request with n_splits > 1 needs T * nq * n_splits * (head_dim + 2) floats of the array.  Larger
+//     requests are refused with BFLY_EINVAL and a message that states both numbers; nothing is launched.
+//     n_splits == 1 writes the output directly and uses no scratch, so it has no such limit.
 //   * The first call on a given device looks up the array's device address (cudaGetSymbolAddress) with
-//     that device current and remembers it.  Make that first call during start-up, before any stream
-//     capture is begun on that device.
+//     that device current and remembers it.  Make that first call before any stream capture is begun
+//     on that device.
 //   * All calls on a device share the one array and it keeps whatever the previous call left in it.
 //     Nothing in it needs to start at zero: every slot a call reads has been written by the same call
 //     first (each split's CTA writes its slice before the merge kernel reads it).  Two calls whose
 //     kernels overlap on the GPU (different streams, or different host threads) race on the array and
 //     produce garbage -- serialise them.
-//   * No cudaMalloc, cudaFree or other allocating call is made on any path of this function.
+//   * After that first call, no path of this function obtains or releases device memory: it makes no
+//     cudaMalloc / cudaFree call and uses no library routine that does.
 //
 // The reference has no counterpart (it has no code at all); this is an addition of this library.
 #include <mutex>
@@ -49,7 +56,13 @@ int scratch_for_current_device(float** out) {
   std::lock_guard<std::mutex> lock(g_scratch_mutex);
   if (g_scratch_addr[dev] == nullptr) {
     float* p = nullptr;
-    BFLY_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_attn_static_scratch));
+    const cudaError_t err = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_attn_static_scratch);
+    if (err != cudaSuccess) {
+      bfly::set_error(std::string("attn_decode_static: cannot place the built-in scratch array on device ") +
+                      std::to_string(dev) + " (it needs " + std::to_string(kStaticScratchBytes >> 20) +
+                      " MiB of free device memory on first use): " + cudaGetErrorString(err));
+      return BFLY_ECUDA;
+    }
     BFLY_CHECK(p != nullptr, "attn_decode_static: cudaGetSymbolAddress returned a null address");
     g_scratch_addr[dev] = p;
   }
@@ -69,10 +82,11 @@ extern "C" int bfly_k_attn_decode_static(const void* q_bf16, const void* kv_page
     BFLY_CHECK(T > 0 && nq > 0 && n_splits >= 1 && head_dim > 0 && S > 0, "attn_decode_static: empty shape");
     const size_t slots = (size_t)T * (size_t)nq * (size_t)n_splits;
     const size_t need = slots * ((size_t)head_dim + 2);
-    if (need > kStaticScratchFloats) {
+    if (n_splits > 1 && need > kStaticScratchFloats) {       // a single split writes bf16 directly: no scratch
       set_error("attn_decode_static: T*nq*n_splits*(head_dim+2) = " + std::to_string(need) +
-                " floats of scratch needed, the built-in array holds " + std::to_string(kStaticScratchFloats) +
-                " (4 MiB); lower n_splits or the batch, or use bfly_k_attn_decode with your own scratch");
+                " floats of scratch needed, the built-in array holds " + std::to_string(kStaticScratchFloats) + " (" +
+                std::to_string(kStaticScratchBytes >> 20) +
+                " MiB); lower n_splits or the batch, or use bfly_k_attn_decode with your own scratch");
       return BFLY_EINVAL;
     }
     float* scratch = nullptr;

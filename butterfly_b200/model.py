@@ -112,6 +112,10 @@ class Model:
         buf = (C.c_char * 128).from_buffer_copy(obj[0])
         self._check(self.lib.bfly_comm_init(self.ctx, buf, self.plan.tp, self.rank))
 
+    def set_ar_mode(self, mode: int):
+        """Decode all-reduce over peer memory: -1 by size, 0 one-shot, 1 two-shot; the same on every rank."""
+        self._check(self.lib.bfly_set_ar_mode(self.ctx, int(mode)))
+
     # ---- forward --------------------------------------------------------------------------------
     def set_page_table(self, table: torch.Tensor):
         t = table.to(torch.int32).contiguous()

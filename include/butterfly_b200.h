@@ -86,6 +86,12 @@ int bfly_weights_ready(bfly_ctx* ctx);   /* validates names/shapes; required bef
 int bfly_comm_unique_id(void* out_id128);                       /* rank 0; 128 bytes */
 int bfly_comm_init(bfly_ctx* ctx, const void* id128, int world, int rank);
 
+/* Mode of the decode-time all-reduce over peer memory (tp > 1): -1 = chosen by size (two-shot when the
+ * rows of one call total >= 1 MiB and tp >= 4), 0 = one-shot (every rank pushes its rows to every rank),
+ * 1 = two-shot (row r is reduced by rank r % tp and pushed back).  Both modes add in rank order, so results
+ * are bit-identical.  Call it at a quiescent point with the SAME value on every rank. */
+int bfly_set_ar_mode(bfly_ctx* ctx, int mode);
+
 /* ---- forward ------------------------------------------------------------------------------- */
 /* Optional: install a page table int32[n_seqs][pages_per_seq] (default: sequence b owns pages
  * b*pages_per_seq ...).  Physical page ids must be unique and < max_batch*pages_per_seq. */
@@ -131,6 +137,11 @@ int bfly_k_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, con
 int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
                        int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int T, int nq,
                        float* part_o, float* part_ml, int n_splits, void* out_bf16, void* stream);
+/* The context split the engine uses for a decode forward of T rows (0 on bad arguments): callers of
+ * bfly_k_attn_decode size part_o = T*nq*n_splits*head_dim and part_ml = T*nq*n_splits*2 floats from it.
+ * S > 1 is allowed (token s of sequence b attends to seq_lens[b] + s + 1 cached positions); seq_lens and
+ * the page table must not be written by the kernel that precedes the call on the stream. */
+int bfly_k_attn_decode_splits(int T, int kv_local, int max_ctx);
 /* Causal attention of S new tokens per sequence (q is [B*S][nq*head_dim]); token s of sequence b sits at
  * position seq_lens[b] + s and sees keys 0 .. seq_lens[b] + s, which must already be in the cache. */
 int bfly_k_attn_prefill(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
@@ -138,12 +149,15 @@ int bfly_k_attn_prefill(const void* q_bf16, const void* kv_pages_bf16, const int
                         void* out_bf16, void* stream);
 /* Same computation as bfly_k_attn_decode for callers that cannot supply or allocate the split-context
  * scratch (the host application's pool owns all of the GPU's memory, cudaMalloc is banned from the
- * hot path, or a binding forwards only inputs and outputs).  The scratch is a fixed 4 MiB array inside
- * the library, present on every GPU that loads it until the process exits.  Needs
- * T*nq*n_splits*(head_dim+2) floats <= 1,048,576, otherwise BFLY_EINVAL and nothing runs.  Allocates
- * nothing.  The first call on a device resolves the array's address: make it at start-up, before any
- * stream capture on that device.  Calls on one device share the array (contents of the previous call
- * remain; nothing needs zeroing); calls that overlap on the GPU race -- serialise them.
+ * hot path, or a binding forwards only inputs and outputs).  The scratch is a fixed 4 MiB array in the
+ * library's device code, one per GPU.  With n_splits > 1 a call needs T*nq*n_splits*(head_dim+2) floats
+ * <= 1,048,576, otherwise BFLY_EINVAL and nothing runs; n_splits == 1 uses no scratch and has no limit.
+ * The first call on a device resolves the array's address, which (CUDA loads device code lazily) is also
+ * when the 4 MiB are claimed on that GPU: make that call at start-up, before your pool takes the rest of
+ * the memory and before any stream capture on that device; it returns BFLY_ECUDA if the memory is not
+ * there.  Later calls obtain and release no device memory.  Calls on one device share the array
+ * (contents of the previous call remain; nothing needs zeroing); calls that overlap on the GPU race --
+ * serialise them.
  * No counterpart in the reference: this entry point is an addition of this library. */
 int bfly_k_attn_decode_static(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table,
                               int pages_per_seq, int page_size, int kv_local, int head_dim, const int32_t* seq_lens,

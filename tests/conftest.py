@@ -15,12 +15,6 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
 
 
-def pytest_collection_modifyitems(config, items):
-    # -m gpu tests must fail loudly, never skip silently, when selected; when no GPU is present and
-    # the marker was not requested explicitly they are simply deselected by -m "not gpu".
-    pass
-
-
 @pytest.fixture(scope="session")
 def cuda():
     import torch

@@ -138,7 +138,8 @@ def test_gemm_split_slices(lib, cuda, M, N, K):
         got = out[:used.value].sum(0).cpu()
         assert not torch.isnan(got).any(), f"unwritten outputs with splits={used.value}"
         err = (got - want).abs().max().item()
-        assert err < 2e-3 * max(1.0, want.abs().max().item()), f"splits={used.value} max err {err}"
+        # bf16-exact inputs, fp32 accumulation on both sides: only the summation order differs
+        assert err < 2e-4 * want.abs().max().item(), f"splits={used.value} max err {err}"
 
 
 @pytest.mark.parametrize("N,K,n_blocks,fb,splits,routed", [

@@ -42,3 +42,23 @@ def test_offsets_are_a_bijection_inside_a_block(d):
     ks = {k_offset(s, x, d) for s in range(ps) for x in range(d)}
     vs = {v_offset(s, x, d) for s in range(ps) for x in range(d)}
     assert ks == set(range(ps * d)) and vs == set(range(ps * d))
+
+
+def test_attention_scratch_sizing_covers_every_row_count():
+    """The decode context-split rule (bfly_k_attn_decode_splits) is not monotone in the row count T, so a
+    scratch sized from samples of T can be too small for the values in between (the engine now takes the
+    maximum over every T; this sweep is the property it relies on, and shows that sampling was unsafe)."""
+    from butterfly_b200 import _lib
+    lib = _lib.load()
+    nq, d = 8, 128
+    unsafe = 0
+    for kv_local, max_ctx, max_t in ((1, 4096, 192), (1, 640, 128), (2, 2048, 96), (8, 2048, 64)):
+        need = [t * nq * lib.bfly_k_attn_decode_splits(t, kv_local, max_ctx) * d for t in range(1, max_t + 1)]
+        assert min(need) > 0
+        cap_all = max(need)
+        sampled = [t for t in range(1, max_t + 1) if t < 64 or t % 64 == 0 or t == max_t]      # round-1 rule
+        cap_sampled = max(need[t - 1] for t in sampled)
+        assert all(n <= cap_all for n in need)
+        unsafe += int(any(n > cap_sampled for n in need))
+    assert unsafe >= 1, "expected at least one geometry where sampled sizing under-allocates"
+    assert lib.bfly_k_attn_decode_splits(0, 1, 128) == 0
