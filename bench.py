@@ -37,6 +37,16 @@ WORKLOAD = "llama3-8b bf16 greedy decode, batch 32, ctx 2048 (BASELINE.json conf
 OTHER_WORKLOADS = {"llama3-70b": (64, 4096), "mixtral-8x7b": (32, 2048), "gpt2-small": (1, 64)}
 
 
+def tensor_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        if "bf16_tflops_sustained" in d:
+            return float(d["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+    return 2250.0, "fallback (nominal dense bf16 2.25 PFLOP/s)"
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -93,69 +103,103 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the oracle on the host cores, bounded sample
 # --------------------------------------------------------------------------------------------------
-def cpu_decode_sample(n_layers_sample: int = 4, steps: int = 3, ctx: int = CTX, batch: int = BATCH):
-    """Times the oracle's decode step at full Llama-3-8B width on `n_layers_sample` of the 32 layers
-    plus the LM head, with a KV cache of `ctx` tokens per sequence already in place, and scales the
-    layer part to 32 layers.  Returns (tokens/s extrapolated, description, cores)."""
-    from butterfly_b200 import LLAMA3_8B, make_plan
-    from butterfly_b200.weights import RankWeights, shard_spec
-    from oracle import OracleModel
+def _mem_available_gb() -> float:
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
 
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    full = LLAMA3_8B
-    cfg = full.with_layers(n_layers_sample)
-    plan = make_plan(cfg, 1)
-    g = torch.Generator().manual_seed(0)
-    tensors = {}
-    base = (torch.randn(1 << 22, generator=g) * 0.02).to(torch.bfloat16)
-    for st in shard_spec(plan, 0):            # same shapes as the GPU arm; values are irrelevant to timing
-        n = st.rows * st.cols
-        t = base.repeat((n + base.numel() - 1) // base.numel())[:n].reshape(st.rows, st.cols)
-        tensors[st.name] = t.reshape(-1) if st.cols == 1 else t
-    om = OracleModel(plan, [RankWeights(plan, 0, tensors)])
-    for l in range(cfg.n_layers):              # a cache of `ctx` tokens per sequence, with room to append
-        om.k_cache[l][0] = torch.randn((batch, ctx + 16, cfg.n_kv_heads, cfg.head_dim), generator=g)
-        om.v_cache[l][0] = torch.randn((batch, ctx + 16, cfg.n_kv_heads, cfg.head_dim), generator=g)
-    om.pos = ctx
-    tok = torch.randint(0, cfg.vocab, (batch,), generator=g, dtype=torch.int32)
-    om.decode(tok)                             # warm-up
-    om.pos = ctx
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        om.pos = ctx                           # every timed step attends over exactly `ctx` cached tokens
-        om.decode(tok)
-    t_sample = (time.perf_counter() - t0) / steps
-    # LM head + embedding share, timed separately so only the layer part is scaled
-    hn = torch.randn((batch, cfg.hidden))
-    w = om.w[0]["lm_head"]
-    t1 = time.perf_counter()
-    for _ in range(steps):
-        _ = hn @ w.t()
-    t_head = (time.perf_counter() - t1) / steps
-    t_layers = max(t_sample - t_head, 1e-9) / n_layers_sample
-    t_full = t_layers * full.n_layers + t_head
-    sample = (f"oracle decode step, full width, {n_layers_sample}/32 layers + LM head timed over {steps} steps at "
-              f"B={batch} ctx={ctx}; layer time scaled x{full.n_layers // n_layers_sample} (extrapolated)")
-    return batch / t_full, sample, cores, t_full
+
+class CpuDecode:
+    """The oracle's decode step of the FULL Llama-3-8B shape (32 layers + LM head, B=32, a KV cache of `ctx`
+    tokens per sequence already in place) on the host cores.  Weight VALUES do not matter for timing, so they are
+    a repeated random block; when the host cannot hold the 32 GB of fp32 weights (+17 GB of fp32 KV), the 32
+    layer applications cycle through `distinct` sets of weights and caches (4 sets = 3.5 GB of weights, far
+    beyond any CPU cache), which leaves flops and bytes per step unchanged."""
+
+    def __init__(self, ctx: int = CTX, batch: int = BATCH):
+        from butterfly_b200 import LLAMA3_8B, make_plan
+        from butterfly_b200.weights import RankWeights, shard_spec
+        from oracle import OracleModel
+
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        full = LLAMA3_8B
+        self.avail_gb = _mem_available_gb()
+        self.distinct = full.n_layers if self.avail_gb >= 80.0 else 4
+        cfg = full.with_layers(self.distinct)
+        plan = make_plan(cfg, 1)
+        g = torch.Generator().manual_seed(0)
+        tensors = {}
+        base = (torch.randn(1 << 22, generator=g) * 0.02).to(torch.bfloat16)
+        for st in shard_spec(plan, 0):            # same shapes as the GPU arm
+            n = st.rows * st.cols
+            t = base.repeat((n + base.numel() - 1) // base.numel())[:n].reshape(st.rows, st.cols)
+            tensors[st.name] = t.reshape(-1) if st.cols == 1 else t
+        om = OracleModel(plan, [RankWeights(plan, 0, tensors)])
+        del tensors
+        for l in range(cfg.n_layers):              # a cache of `ctx` tokens per sequence, with room to append
+            om.k_cache[l][0] = torch.randn((batch, ctx + 16, cfg.n_kv_heads, cfg.head_dim), generator=g)
+            om.v_cache[l][0] = torch.randn((batch, ctx + 16, cfg.n_kv_heads, cfg.head_dim), generator=g)
+        if self.distinct < full.n_layers:          # layer l runs on the weights and cache of set l % distinct
+            w = om.w[0]
+            for l in range(self.distinct, full.n_layers):
+                for name in [k for k in w if k.startswith("layers.0.")]:
+                    w[f"layers.{l}." + name[len("layers.0."):]] = w[f"layers.{l % self.distinct}." + name[len("layers.0."):]]
+                om.k_cache.append(om.k_cache[l % self.distinct])
+                om.v_cache.append(om.v_cache[l % self.distinct])
+            om.cfg = full
+            om.plan = make_plan(full, 1)
+        self.om, self.ctx, self.batch, self.layers = om, ctx, batch, full.n_layers
+        self.tok = torch.randint(0, full.vocab, (batch,), generator=g, dtype=torch.int32)
+
+    def step(self) -> float:
+        self.om.pos = self.ctx                     # every step attends over exactly `ctx` cached tokens
+        t0 = time.perf_counter()
+        self.om.decode(self.tok)
+        return time.perf_counter() - t0
+
+    def describe(self, steps: int) -> str:
+        how = ("32 distinct layers" if self.distinct == self.layers else
+               f"32 layer applications cycling through {self.distinct} distinct weight/KV sets "
+               f"(host has {self.avail_gb:.0f} GB available; same flops and bytes per step)")
+        return (f"oracle (CPU fp32 PyTorch) decode step of the full llama3-8b shape, {how}, + LM head, B={self.batch} "
+                f"ctx={self.ctx}, random weights, {steps} timed steps, {self.cores} threads")
 
 
 def run_reference(args):
+    """The stand-in reference (the reference repository has no code): every one of the --steps steps is a real,
+    full-cost decode step of the oracle on the host cores; nothing is extrapolated."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 3))
-    value, sample, cores, t_full = cpu_decode_sample(steps=steps)
+    cpu = CpuDecode()
+    for _ in range(args.warmup):
+        cpu.step()
+    times = [cpu.step() for _ in range(args.steps)]
+    total = sum(times)
+    value = BATCH * args.steps / total
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": t_full * 1e3, "higher_is_better": True, "scaling": "strong",
+        "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "global_batch": BATCH, "ctx": CTX, "parallelism": "cpu"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": gpu_config("llama3-8b", 32, max(1, args.gpus)),
+        "extrapolated": False, "layers_timed": cpu.layers, "distinct_weight_sets": cpu.distinct,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "kind": "port", "sample": cpu.describe(args.steps)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "the reference repository has no implementation; this is the CPU fp32 oracle that stands in for it",
+        "note": "the reference repository has no implementation; this is the CPU fp32 oracle that stands in for it "
+                "(config.parallelism names the GPU arm's layout; this arm runs on the host cores only)",
     }
     print(json.dumps(line), flush=True)
+
+
+def gpu_config(model: str, layers: int, tp: int) -> dict:
+    return {"workload": WORKLOAD, "model": model, "global_batch": BATCH, "ctx": CTX, "parallelism": f"tp{tp}",
+            "l2": "inputs_exceed_l2 (weights+KV per step >> 126 MB)", "layers": layers}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -235,6 +279,105 @@ def measure_decode_attention(lib, batch, ctx, nq, nk, d, max_ctx, iters=12):
             "algo_bytes_per_launch": algo_bytes, "achieved": algo_bytes / ms / 1e6, "unit": "GB/s", "bound": "hbm"}
 
 
+def source_sha16(*names) -> str:
+    """Identifies the kernel source a committed ncu traffic figure belongs to (git is not on the GPU box)."""
+    import hashlib
+    h = hashlib.sha256()
+    for n in names:
+        with open(os.path.join(ROOT, "butterfly_b200", "csrc", n), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def committed_traffic(kernel_key: str, shape, sources):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+    (profiles/r02_traffic.json: one entry per (kernel, shape), with the sha of the kernel source it was taken
+    from).  Returns (bytes or None, source file or None, stale flag)."""
+    path = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    try:
+        with open(path) as f:
+            table = json.load(f)
+    except (OSError, ValueError):
+        return None, None, None
+    for e in table.get("entries", []):
+        if e.get("kernel") == kernel_key and list(e.get("shape", [])) == list(shape):
+            return e.get("dram_bytes"), e.get("from"), e.get("source_sha16") != source_sha16(*sources)
+    return None, None, None
+
+
+def parity_leg(dist, world, rank, local):
+    """Before anything is timed: the same engine, communicator layout and all-reduce modes as the timed run,
+    against the CPU fp32 oracle (rank 0 holds all `world` rank shards in-process and broadcasts the teacher
+    tokens).  Uses the oracle strictly as the checker.  Returns the `parity` object; any failure aborts."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from parity_gates import LOGIT_TOL, REL_MAX, REL_RMS, Gate
+    from butterfly_b200 import LLAMA3_8B, LLAMA3_70B, Model, SyntheticSource, make_plan, shard_weights, synthetic_tokens
+    import hashlib
+    cases = [("llama3-8b width, 2 layers, B=4, prefill 48 + 4 teacher-forced steps", LLAMA3_8B.with_layers(2), 4, 48, 4,
+              (0, 1) if world > 1 else (-1,))]
+    if world >= 4:     # 64 x 8192 fp32 decode rows = 2 MiB per call: the size rule (-1) picks two-shot by itself
+        cases.append(("llama3-70b width, 1 layer, B=64 (2 MiB per all-reduce), prefill 8 + 3 steps",
+                      LLAMA3_70B.with_layers(1), 64, 8, 3, (-1, 0, 1)))
+    out, worst = [], Gate()
+    mode_name = {-1: "by_size", 0: "one_shot", 1: "two_shot"}
+    for name, cfg, B, S, steps, modes in cases:
+        plan = make_plan(cfg, world)
+        src = SyntheticSource(cfg, 0)
+        toks = synthetic_tokens(cfg, B, S)
+        gm = Model(plan, rank, src, device=local, max_batch=B, max_ctx=S + steps + 8)
+        gm.connect()
+        want = None
+        if rank == 0:
+            from oracle import OracleModel
+            om = OracleModel(plan, [shard_weights(src, plan, r) for r in range(world)])
+            want, teacher = [om.prefill(toks)], []
+            for _ in range(steps):
+                t = om.last_tokens.clone()
+                teacher.append(t)
+                want.append(om.decode(t))
+            del om
+        else:
+            teacher = None
+        if dist is not None:
+            box = [teacher]
+            dist.broadcast_object_list(box, src=0)
+            teacher = box[0]
+        got = {}
+        for m in modes:
+            gm.set_ar_mode(m)
+            got[m] = [gm.prefill(toks)] + [gm.decode(t) for t in teacher]
+        gm.close()
+        digest = {m: hashlib.sha256(b"".join(x.numpy().tobytes() for x in got[m])).hexdigest() for m in modes}
+        all_digests = [digest]
+        if dist is not None:
+            all_digests = [None] * world
+            dist.all_gather_object(all_digests, digest)
+        if rank == 0:
+            entry = {"case": name, "tp": world, "ar_modes": [mode_name[m] for m in modes] if world > 1 else ["none (tp=1)"]}
+            for m in modes:
+                g = Gate()
+                for a, b in zip(got[m], want):
+                    g.add(a, b)
+                    worst.add(a, b)
+                entry[f"max_abs_dlogit_{mode_name[m]}"] = g.max_abs
+                entry[f"max_rel_sigma_{mode_name[m]}"] = g.max_rel
+                entry[f"rms_rel_sigma_{mode_name[m]}"] = g.rms_rel
+                g.check(f"bench parity leg: {name}, all-reduce {mode_name[m]}")
+            ranks_equal = all(dg == all_digests[0] for dg in all_digests)
+            modes_equal = len({digest[m] for m in modes if m != modes[0]} | {digest[modes[0]]}) == 1
+            entry["ranks_bit_identical"], entry["ar_modes_bit_identical"] = ranks_equal, modes_equal
+            assert ranks_equal, f"bench parity leg: ranks returned different logits ({name})"
+            assert modes_equal, f"bench parity leg: all-reduce modes differ bitwise ({name})"
+            out.append(entry)
+    if rank != 0:
+        return None
+    modes_seen = sorted({m for e in out for m in e["ar_modes"]})
+    return {"vs": "cpu oracle (fp32, all rank shards in-process on rank 0)", "cases": out,
+            "max_abs_dlogit": worst.max_abs, "max_rel_sigma": worst.max_rel, "rms_rel_sigma": worst.rms_rel,
+            "gates": {"max_abs": LOGIT_TOL, "max_rel_sigma": REL_MAX, "rms_rel_sigma": REL_RMS},
+            "ar_modes": modes_seen}
+
+
 def run_gpu(args):
     from butterfly_b200 import LLAMA3_8B, Model, SyntheticSource, _lib, make_plan, synthetic_tokens
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -258,6 +401,13 @@ def run_gpu(args):
         WORKLOAD = f"{args.model} bf16 greedy decode, batch {BATCH}, ctx {CTX} (BASELINE.json configs; not the headline line)"
     cfg = base_cfg if args.layers <= 0 else base_cfg.with_layers(args.layers)
     tp = world if args.shard_of <= 1 else args.shard_of
+    parity = None
+    if not args.no_parity and args.shard_of <= 1:
+        try:
+            parity = parity_leg(dist, world, rank, local)
+        except AssertionError as exc:               # a fast wrong answer is not a result
+            print(json.dumps({"parity_failure": str(exc)[:400], "n_gpus": world}), flush=True)
+            os._exit(3)
     plan = make_plan(cfg, tp)
     W, K = args.warmup, args.steps
     max_ctx = CTX + 2 * (max(W, 3) + K) + 16
@@ -300,6 +450,16 @@ def run_gpu(args):
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     launches = model.stats()["kernel_launches"] - launches0
+    # the greedy tokens of the K timed steps must be the same bits on every rank
+    import hashlib
+    hist = hashlib.sha256(model.read_history(BATCH, K).numpy().tobytes()).hexdigest()
+    hists = [hist]
+    if dist is not None:
+        hists = [None] * world
+        dist.all_gather_object(hists, hist)
+    if any(h != hists[0] for h in hists):
+        print(json.dumps({"parity_failure": "ranks disagree on the greedy tokens of the timed steps", "n_gpus": world}), flush=True)
+        os._exit(3)
 
     # ---- end to end through the public API with host buffers ----
     pinned_in = torch.zeros((BATCH,), dtype=torch.int32).pin_memory()
@@ -326,44 +486,63 @@ def run_gpu(args):
         value = BATCH * K / (ms / 1e3)
         ctx_mid = CTX + max(W, 3) + K / 2.0
         step_bytes = plan.weight_bytes_per_rank() + plan.kv_bytes_per_token_per_rank() * BATCH * (ctx_mid + 1)
-        gemm = measure_dominant_gemm(lib, plan.ffn_local * (2 if cfg.gated else 1) * max(1, plan.experts_local), BATCH,
-                                     cfg.hidden)
+        gemm_shape = (plan.ffn_local * (2 if cfg.gated else 1) * max(1, plan.experts_local), BATCH, cfg.hidden)
+        gemm = measure_dominant_gemm(lib, *gemm_shape)
+        attn = measure_decode_attention(lib, BATCH, CTX, plan.q_local, plan.kv_local, cfg.head_dim, model.max_ctx)
+        # the roofline object describes the kernel with the largest share of the step
+        share_gemm = gemm["ms"] * cfg.n_layers / ms_step
+        share_attn = attn["kernel_ms"] * cfg.n_layers / ms_step
+        if share_attn >= share_gemm:
+            kname, kms, kbytes, kshape = attn["kernel"], attn["kernel_ms"], attn["algo_bytes_per_launch"], \
+                [BATCH, CTX, plan.q_local, plan.kv_local, cfg.head_dim]
+            traffic, tsrc, stale = committed_traffic("attn_decode", kshape, ["attn_decode.cu", "attn_common.cuh"])
+            kshare, extra = share_attn, {"n_splits": attn["n_splits"]}
+        else:
+            kname, kms, kbytes, kshape = gemm["kernel"], gemm["ms"], gemm["algo_bytes"], list(gemm["shape"])
+            traffic, tsrc, stale = committed_traffic("gemm_gate_up", kshape, ["gemm_tcgen05.cu", "tcgen05_common.cuh"])
+            kshare, extra = share_gemm, {"splits": gemm["splits"]}
+        achieved = kbytes / kms / 1e6
+        flops = plan.prefill_flops(BATCH, CTX) if hasattr(plan, "prefill_flops") else None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "model": cfg.name, "global_batch": BATCH, "ctx": CTX,
-                       "parallelism": f"tp{tp}", "l2": "inputs_exceed_l2 (weights+KV per step >> 126 MB)",
-                       "layers": cfg.n_layers},
+            "config": gpu_config(cfg.name, cfg.n_layers, tp),
             "e2e": {"value": BATCH * K / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 4,
                     "d2h_bytes_per_step": BATCH * 4},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "achieved": gemm["gbs"], "peak": hbm_peak, "unit": "GB/s",
-                         "frac": gemm["gbs"] / hbm_peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the committed
-                         # `ncu --set full` capture (profiles/r01_ncu_full_gemm_attn.txt): 235.17 + 3.96 MB
-                         "traffic": 239129344 if (tp == 1 and cfg.n_layers == 32) else None,
-                         "traffic_source": "profiles/r01_ncu_full_gemm_attn.txt", "peak_source": peak_src,
-                         "kernel": gemm["kernel"], "shape_MNK": gemm["shape"], "splits": gemm["splits"],
-                         "kernel_ms": gemm["ms"], "algo_bytes_per_launch": gemm["algo_bytes"]},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": tsrc,
+                         "traffic_stale": stale, "peak_source": peak_src, "kernel": kname, "shape": kshape,
+                         "kernel_ms": kms, "algo_bytes_per_launch": kbytes, "share_of_step": kshare,
+                         "launches_per_step": cfg.n_layers, **extra},
+            "roofline_gemm": {"kernel": gemm["kernel"], "shape_MNK": gemm["shape"], "splits": gemm["splits"],
+                              "kernel_ms": gemm["ms"], "algo_bytes_per_launch": gemm["algo_bytes"],
+                              "achieved": gemm["gbs"], "frac": gemm["gbs"] / hbm_peak, "share_of_step": share_gemm},
+            "roofline_attention": {**attn, "peak": hbm_peak, "frac": attn["achieved"] / hbm_peak,
+                                   "share_of_step": share_attn},
             "step_roofline": {"algo_bytes_per_step_per_gpu": step_bytes, "achieved_gbs_per_gpu": step_bytes / ms_step / 1e6,
                               "frac_of_hbm_peak": step_bytes / ms_step / 1e6 / hbm_peak},
             "prefill": {"tokens_per_s": BATCH * CTX / (prefill_ms / 1e3), "ms": prefill_ms, "tokens": BATCH * CTX},
+            "parity": parity,
+            "ranks_agree_on_timed_tokens": True,
             "setup_s": setup_s,
         }
-        try:                                             # second-largest kernel; never allowed to cost the line
-            attn = measure_decode_attention(lib, BATCH, CTX, plan.q_local, plan.kv_local, cfg.head_dim, model.max_ctx)
-            attn["peak"], attn["frac"] = hbm_peak, attn["achieved"] / hbm_peak
-            line["roofline_attention"] = attn
-        except Exception as exc:                         # noqa: BLE001
-            line["roofline_attention"] = {"error": str(exc)[:200]}
+        if flops is not None:
+            tf_peak = tensor_peak()
+            tf = flops / world / (prefill_ms / 1e3) / 1e12
+            line["roofline_prefill"] = {"bound": "tensor", "algo_flops": flops, "achieved": tf, "peak": tf_peak[0],
+                                        "unit": "TFLOP/s per GPU", "frac": tf / tf_peak[0], "peak_source": tf_peak[1]}
         if args.shard_of > 1:
             line["INVALID"] = (f"profiling run: rank 0's shard of a tp={tp} plan on one GPU with the collectives "
                                "skipped; per-rank compute time only, results are not a model output")
         if not args.no_cpu and world == 1 and args.shard_of <= 1 and args.model == "llama3-8b":
-            v, sample, cores, _ = cpu_decode_sample()
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+            cpu = CpuDecode()                            # bounded: 1 warm-up + 2 timed full-cost steps (~20 s)
+            cpu.step()
+            t_cpu = [cpu.step() for _ in range(2)]
+            line["cpu_baseline"] = {"value": BATCH * len(t_cpu) / sum(t_cpu), "unit": UNIT, "cores": cpu.cores,
+                                    "kind": "port", "sample": cpu.describe(len(t_cpu))}
         print(json.dumps(line), flush=True)
     model.close()
     if dist is not None:
@@ -379,6 +558,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--layers", type=int, default=0, help="debug: reduce depth (the result is then NOT the headline config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle parity leg (profiling runs only)")
     ap.add_argument("--model", default="llama3-8b", choices=["llama3-8b", "llama3-70b", "mixtral-8x7b", "gpt2-small"],
                     help="shape to run; anything but llama3-8b is an extra (non-headline) line")
     ap.add_argument("--shard-of", type=int, default=0, help="profiling aid: run rank 0's shard of a tp=N plan on one "

@@ -52,6 +52,7 @@ SIGNATURES = {
     "bfly_decode": (i32, [vp, vp, i32, vp, vp]),
     "bfly_decode_greedy": (i32, [vp, i32, i32, vp]),
     "bfly_decode_enqueue": (i32, [vp, i32, i32]),
+    "bfly_read_history": (i32, [vp, i32, i32, vp]),
     "bfly_sync": (i32, [vp]),
     "bfly_stream": (vp, [vp]),
     "bfly_k_fill_synth": (i32, [vp, i64, u64, i64, i64, i64, i64, i64, f32, f32, vp]),

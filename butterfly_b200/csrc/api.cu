@@ -193,6 +193,11 @@ int bfly_decode_enqueue(bfly_ctx* ctx, int B, int n_steps) {
   return guarded(ctx, [&]() -> int { return ctx->engine->decode_enqueue(B, n_steps); });
 }
 
+int bfly_read_history(bfly_ctx* ctx, int B, int n_steps, int32_t* tokens_out_host) {
+  NEED_CTX(ctx);
+  return guarded(ctx, [&]() -> int { return ctx->engine->read_history(B, n_steps, tokens_out_host); });
+}
+
 int bfly_sync(bfly_ctx* ctx) {
   NEED_CTX(ctx);
   return guarded(ctx, [&]() -> int {

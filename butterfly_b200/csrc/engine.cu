@@ -688,18 +688,24 @@ int Engine::decode_enqueue(int B, int n_steps) {
   return BFLY_OK;
 }
 
+// The tokens fed at each step of the last bfly_decode_enqueue / bfly_decode_greedy of B sequences.
+int Engine::read_history(int B, int n_steps, int32_t* tokens_out_host) {
+  BFLY_CHECK(tokens_out_host != nullptr && B >= 1 && B <= d.max_batch && n_steps >= 1 && n_steps <= kMaxGreedySteps,
+             "read_history: shape");
+  BFLY_CUDA(cudaSetDevice(device));
+  // history is [step][B]; the caller wants [B][n_steps]
+  std::vector<int> tmp((size_t)n_steps * B);
+  BFLY_CUDA(cudaMemcpyAsync(tmp.data(), history, tmp.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  for (int s = 0; s < n_steps; ++s)
+    for (int b = 0; b < B; ++b) tokens_out_host[(size_t)b * n_steps + s] = tmp[(size_t)s * B + b];
+  return BFLY_OK;
+}
+
 int Engine::decode_greedy(int B, int n_steps, int32_t* tokens_out_host) {
   BFLY_TRY(decode_enqueue(B, n_steps));
-  if (tokens_out_host) {
-    // history is [step][B]; the caller wants [B][n_steps]
-    std::vector<int> tmp((size_t)n_steps * B);
-    BFLY_CUDA(cudaMemcpyAsync(tmp.data(), history, tmp.size() * sizeof(int), cudaMemcpyDeviceToHost, stream));
-    BFLY_CUDA(cudaStreamSynchronize(stream));
-    for (int s = 0; s < n_steps; ++s)
-      for (int b = 0; b < B; ++b) tokens_out_host[(size_t)b * n_steps + s] = tmp[(size_t)s * B + b];
-  } else {
-    BFLY_CUDA(cudaStreamSynchronize(stream));
-  }
+  if (tokens_out_host) return read_history(B, n_steps, tokens_out_host);
+  BFLY_CUDA(cudaStreamSynchronize(stream));
   return BFLY_OK;
 }
 

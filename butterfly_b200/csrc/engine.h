@@ -105,6 +105,7 @@ struct Engine {
   int decode(const int32_t* tokens_host, int B, float* logits_host, int32_t* next_host);
   int decode_enqueue(int B, int n_steps);
   int decode_greedy(int B, int n_steps, int32_t* tokens_out_host);
+  int read_history(int B, int n_steps, int32_t* tokens_out_host);
 
  private:
   int find(const std::string& name, int64_t rows, int64_t cols, bool required, bf16** out);

@@ -169,6 +169,12 @@ class Model:
     def decode_enqueue(self, batch: int, n_steps: int):
         self._check(self.lib.bfly_decode_enqueue(self.ctx, batch, n_steps))
 
+    def read_history(self, batch: int, n_steps: int) -> torch.Tensor:
+        """Tokens fed at each step of the last decode_enqueue / decode_greedy: int32[B, n_steps]."""
+        out = torch.empty((batch, n_steps), dtype=torch.int32)
+        self._check(self.lib.bfly_read_history(self.ctx, batch, n_steps, out.data_ptr()))
+        return out
+
     def sync(self):
         self._check(self.lib.bfly_sync(self.ctx))
 

@@ -105,6 +105,23 @@ class PartitionPlan:
         head = self.vocab_shard * c.hidden
         return 2 * (c.n_layers * (attn + ffn) + head)
 
+    def prefill_flops(self, batch: int, seq: int) -> int:
+        """Algorithmic flops of one prefill over the whole TP group: 2 * tokens * the
+        parameters of the linear layers a token passes through (top-k experts for MoE) + causal attention
+        (2 * n_heads * head_dim * S^2 per layer and sequence: QK^T and PV over S^2/2 pairs) + the LM head on the
+        last token of every sequence."""
+        c = self.cfg
+        d = c.head_dim
+        attn_lin = (c.n_heads + 2 * c.n_kv_heads) * d * c.hidden + c.hidden * c.n_heads * d
+        if c.is_moe:
+            ffn = c.top_k * 3 * c.hidden * c.ffn + c.n_experts * c.hidden
+        else:
+            ffn = (3 if c.gated else 2) * c.hidden * c.ffn
+        linear = 2 * batch * seq * c.n_layers * (attn_lin + ffn)
+        attention = 2 * c.n_heads * d * seq * seq * c.n_layers * batch
+        head = 2 * batch * c.vocab * c.hidden
+        return linear + attention + head
+
     def kv_bytes_per_token_per_rank(self) -> int:
         """bf16 K+V bytes one rank holds per cached token over all layers."""
         return 2 * 2 * self.cfg.n_layers * self.kv_local * self.cfg.head_dim

@@ -115,6 +115,9 @@ int bfly_decode(bfly_ctx* ctx, const int32_t* tokens_host, int B, float* logits_
 int bfly_decode_greedy(bfly_ctx* ctx, int B, int n_steps, int32_t* tokens_out_host);
 /* Same, but only enqueues the steps on the ctx stream (for device-side timing); no copy, no sync. */
 int bfly_decode_enqueue(bfly_ctx* ctx, int B, int n_steps);
+/* The tokens fed at the n_steps steps of the LAST bfly_decode_enqueue / bfly_decode_greedy of B sequences
+ * (int32[B][n_steps]); synchronises the ctx stream. */
+int bfly_read_history(bfly_ctx* ctx, int B, int n_steps, int32_t* tokens_out_host);
 int bfly_sync(bfly_ctx* ctx);
 void* bfly_stream(bfly_ctx* ctx);        /* the ctx's cudaStream_t, for event timing by the caller */
 
