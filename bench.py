@@ -318,7 +318,7 @@ def parity_leg(dist, world, rank, local):
     if world >= 4:     # 64 x 8192 fp32 decode rows = 2 MiB per call: the size rule (-1) picks two-shot by itself
         cases.append(("llama3-70b width, 1 layer, B=64 (2 MiB per all-reduce), prefill 8 + 3 steps",
                       LLAMA3_70B.with_layers(1), 64, 8, 3, (-1, 0, 1)))
-    out, worst = [], Gate()
+    out, worst = [], Gate(2)
     mode_name = {-1: "by_size", 0: "one_shot", 1: "two_shot"}
     for name, cfg, B, S, steps, modes in cases:
         plan = make_plan(cfg, world)
@@ -355,7 +355,7 @@ def parity_leg(dist, world, rank, local):
         if rank == 0:
             entry = {"case": name, "tp": world, "ar_modes": [mode_name[m] for m in modes] if world > 1 else ["none (tp=1)"]}
             for m in modes:
-                g = Gate()
+                g = Gate(cfg.n_layers)
                 for a, b in zip(got[m], want):
                     g.add(a, b)
                     worst.add(a, b)

@@ -47,12 +47,14 @@ SIGNATURES = {
     "bfly_comm_init": (i32, [vp, vp, i32, i32]),
     "bfly_set_page_table": (i32, [vp, vp, i32, i32]),
     "bfly_set_ar_mode": (i32, [vp, i32]),
+    "bfly_bench_allreduce": (i32, [vp, i32, i32, C.POINTER(f32), C.POINTER(f32)]),
     "bfly_prefill": (i32, [vp, vp, i32, i32, vp, vp]),
     "bfly_prefill_at": (i32, [vp, i32, vp, i32, i32, vp, vp]),
     "bfly_decode": (i32, [vp, vp, i32, vp, vp]),
     "bfly_decode_greedy": (i32, [vp, i32, i32, vp]),
     "bfly_decode_enqueue": (i32, [vp, i32, i32]),
     "bfly_read_history": (i32, [vp, i32, i32, vp]),
+    "bfly_read_step_trace": (i32, [vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]),
     "bfly_sync": (i32, [vp]),
     "bfly_stream": (vp, [vp]),
     "bfly_k_fill_synth": (i32, [vp, i64, u64, i64, i64, i64, i64, i64, f32, f32, vp]),

@@ -19,7 +19,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "_obj")
 LIB = os.path.join(HERE, "libbutterfly_b200.so")
 SOURCES = ["api.cu", "engine.cu", "synth.cu", "elementwise.cu", "attn_decode.cu", "attn_prefill.cu",
-           "gemm_tcgen05.cu", "allreduce_norm.cu", "noalloc.cu"]
+           "gemm_tcgen05.cu", "allreduce_norm.cu", "noalloc.cu", "decode_step.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -164,6 +164,19 @@ int bfly_set_ar_mode(bfly_ctx* ctx, int mode) {
   return guarded(ctx, [&]() -> int { return ctx->engine->set_ar_mode(mode); });
 }
 
+int bfly_read_step_trace(bfly_ctx* ctx, uint64_t* out_ns, int max_entries, int* n_entries, int* attn_splits) {
+  NEED_CTX(ctx);
+  return guarded(ctx, [&]() -> int {
+    BFLY_CHECK(out_ns && n_entries && attn_splits && max_entries > 0, "read_step_trace: arguments");
+    return ctx->engine->read_step_trace(reinterpret_cast<unsigned long long*>(out_ns), max_entries, n_entries, attn_splits);
+  });
+}
+
+int bfly_bench_allreduce(bfly_ctx* ctx, int T, int iters, float* us_allreduce, float* us_plain) {
+  NEED_CTX(ctx);
+  return guarded(ctx, [&]() -> int { return ctx->engine->bench_allreduce(T, iters, us_allreduce, us_plain); });
+}
+
 int bfly_prefill(bfly_ctx* ctx, const int32_t* tokens_host, int B, int S, float* logits_host,
                  int32_t* next_tokens_host) {
   NEED_CTX(ctx);

@@ -137,6 +137,10 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     e->fused_swiglu = !(env && env[0] == '0');
     env = getenv("BFLY_MOE_GROUPED");                   // tuning knob; default on
     e->moe_grouped = !(env && env[0] == '0') && e->gated && e->fused_swiglu;
+    // The fused decode step kernel (decode_step.cu) is parity-green but measured SLOWER than the kernel-per-op
+    // path so far, so it is opt-in: BFLY_FUSED_STEP=1.
+    env = getenv("BFLY_FUSED_STEP");
+    e->fused_step = env && env[0] == '1';
     env = getenv("BFLY_AR_TWO_SHOT");                   // initial all-reduce mode; bfly_set_ar_mode() changes it
     e->ar_mode = env ? (env[0] == '1' ? 1 : 0) : -1;
   }
@@ -352,7 +356,8 @@ int Engine::comm_init(const void* id128, int world, int rank) {
 // the CUDA IPC handles travel through an NCCL all-gather, and each rank maps its peers' buffers.
 int Engine::p2p_init() {
   const int tp = d.tp, max_rows = d.max_batch, h = d.hidden;
-  const size_t flags_bytes = (((size_t)2 * tp * max_rows * sizeof(unsigned)) + 255) / 256 * 256;
+  const size_t row_flags_bytes = (((size_t)2 * tp * max_rows * sizeof(unsigned)) + 255) / 256 * 256;
+  const size_t flags_bytes = row_flags_bytes * 9;        // per-row flags, then 8 per-chunk flags per row
   const size_t recv_bytes = (size_t)2 * tp * max_rows * h * sizeof(float);
   char* base = nullptr;
   BFLY_TRY(dev_alloc(this, &base, flags_bytes + recv_bytes, &workspace_bytes));
@@ -380,6 +385,7 @@ int Engine::p2p_init() {
       p = (char*)q;
     }
     ar.flags[r] = (unsigned*)p;
+    ar.cflags[r] = (unsigned*)(p + row_flags_bytes);
     ar.recv[r] = (float*)(p + flags_bytes);
   }
   // nobody starts pushing before every rank has mapped its peers
@@ -582,6 +588,162 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
   return BFLY_OK;
 }
 
+// ---- fused decode step (decode_step.cu) --------------------------------------------------------
+bool Engine::step_supported(int B) const {
+  const bfly_model_desc& c = d;
+  if (!fused_step || c.family != BFLY_FAMILY_LLAMA || c.n_experts != 0 || c.bias != 0 || c.rope_theta <= 0.f) return false;
+  if (c.head_dim != 128 || c.hidden % 128 != 0 || B > kStepMaxTokens || f_block % 4 != 0 || v_local <= 0) return false;
+  if (c.tp > 1 && !p2p_ready && !(comm == nullptr && getenv("BFLY_SKIP_COLLECTIVES"))) return false;
+  if (c.tp > 1 && p2p_ready && B > ar.max_rows) return false;
+  return true;
+}
+
+namespace {
+// stream-K tables of one GEMM: first CTA and number of CTAs (= slices) per weight tile
+int make_step_gemm(Engine* e, int M, int K, int T, int grid, StepGemm* out) {
+  StepGemm g{};
+  g.M = M; g.K = K;
+  g.nkb = ceil_div(K, 64);
+  g.m_tiles = ceil_div(M, 128);
+  g.units = g.m_tiles * g.nkb;
+  g.ge = std::min(grid, g.units);
+  std::vector<unsigned short> first((size_t)g.m_tiles);
+  std::vector<unsigned char> nsl((size_t)g.m_tiles);
+  int max_sl = 1;
+  for (int t = 0; t < g.m_tiles; ++t) {
+    const int a = sk_owner(g, t * g.nkb), b = sk_owner(g, t * g.nkb + g.nkb - 1);
+    first[(size_t)t] = (unsigned short)a;
+    nsl[(size_t)t] = (unsigned char)(b - a + 1);
+    max_sl = std::max(max_sl, b - a + 1);
+  }
+  BFLY_CHECK(max_sl <= 255 && grid <= 65535, "decode_step: too many slices per tile");
+  g.max_slices = max_sl;
+  unsigned short* d_first = nullptr;
+  unsigned char* d_nsl = nullptr;
+  BFLY_TRY(dev_alloc(e, &d_first, first.size(), &e->workspace_bytes));
+  BFLY_TRY(dev_alloc(e, &d_nsl, nsl.size(), &e->workspace_bytes));
+  BFLY_CUDA(cudaMemcpy(d_first, first.data(), first.size() * sizeof(unsigned short), cudaMemcpyHostToDevice));
+  BFLY_CUDA(cudaMemcpy(d_nsl, nsl.data(), nsl.size(), cudaMemcpyHostToDevice));
+  g.first = d_first; g.nsl = d_nsl;
+  BFLY_TRY(dev_alloc(e, &g.out, (size_t)max_sl * T * M, &e->workspace_bytes));
+  *out = g;
+  return BFLY_OK;
+}
+}  // namespace
+
+int Engine::build_step_plan(int B, bool want_logits, StepPlan** out) {
+  const int key = B * 2 + (want_logits ? 1 : 0);
+  auto it = step_plans.find(key);
+  if (it != step_plans.end()) { *out = &it->second; return BFLY_OK; }
+  const bfly_model_desc& c = d;
+  BFLY_CUDA(cudaSetDevice(device));
+  BFLY_TRY(decode_step_init());
+  StepPlan sp{};
+  StepParams& p = sp.p;
+  sp.grid = sm_count;
+  const int T = B, h = c.hidden, dh = c.head_dim;
+  p.T = T;
+  p.bn = std::max(16, ceil_div(T, 16) * 16);
+  p.stages = std::min(10, (int)(kStepRingBytes / (16384 + (size_t)p.bn * 128)));
+  if (const char* env = getenv("BFLY_STEP_STAGES")) p.stages = std::max(2, std::min(p.stages, atoi(env)));   // tuning knob
+  p.n_layers = c.n_layers; p.h = h; p.nq = q_local; p.nk = kv_local; p.f_local = f_block;
+  p.qkv_rows = qkv_rows; p.v_local = v_local; p.v0 = v0; p.vocab = c.vocab;
+  p.eps = c.norm_eps;
+  p.attn_scale_log2 = 1.4426950408889634f / std::sqrt((float)dh);
+  if (const char* env = getenv("BFLY_STEP_TUNE")) p.tune = atoi(env);
+  p.n_producers = 3;
+  if (const char* env = getenv("BFLY_STEP_PRODUCERS")) p.n_producers = std::max(1, std::min(3, atoi(env)));   // A/B knob
+  // norm phases: as many (row, chunk) items as fit the grid, chunks tile-aligned
+  p.chunks = 1;
+  while (p.chunks < 8 && T * p.chunks * 2 <= sp.grid && h % (p.chunks * 2 * 128) == 0) p.chunks *= 2;
+  // context splits of the attention items: fewest rounds x tiles per item (+3 tiles of ramp per item)
+  {
+    const int tiles = std::max(1, ceil_div(c.max_ctx, 32));
+    int best = 1;
+    long best_cost = -1;
+    for (int s = 1; s <= 16 && (s == 1 || tiles / s >= 4); ++s) {
+      const long cost = (long)ceil_div(T * kv_local * s, sp.grid) * (ceil_div(tiles, s) + 3);
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = s; }
+    }
+    p.attn_splits = best;
+  }
+  BFLY_TRY(make_step_gemm(this, qkv_rows, h, T, sp.grid, &p.gemm[SG_QKV]));
+  BFLY_TRY(make_step_gemm(this, h, q_local * dh, T, sp.grid, &p.gemm[SG_WO]));
+  BFLY_TRY(make_step_gemm(this, 2 * f_block, h, T, sp.grid, &p.gemm[SG_GU]));
+  BFLY_TRY(make_step_gemm(this, h, f_block, T, sp.grid, &p.gemm[SG_DOWN]));
+  BFLY_TRY(make_step_gemm(this, v_local, h, T, sp.grid, &p.gemm[SG_HEAD]));
+  // tensor maps
+  const int n_maps = c.n_layers * 4 + 4;
+  std::vector<char> maps((size_t)n_maps * 128);
+  auto M = [&](int i) { return (void*)(maps.data() + (size_t)i * 128); };
+  for (int l = 0; l < c.n_layers; ++l) {
+    const LayerW& w = layers[l];
+    BFLY_TRY(make_tensor_map_2d(M(l * 4 + 0), w.wqkv, qkv_rows, h, h, 128));
+    BFLY_TRY(make_tensor_map_2d(M(l * 4 + 1), w.wo, h, q_local * dh, q_local * dh, 128));
+    BFLY_TRY(make_tensor_map_2d(M(l * 4 + 2), w.w_in, 2 * f_block, h, h, 128));
+    BFLY_TRY(make_tensor_map_2d(M(l * 4 + 3), w.w_down, h, f_block, f_block, 128));
+  }
+  BFLY_TRY(make_tensor_map_2d(M(c.n_layers * 4 + 0), lm_head, v_local, h, h, 128));
+  BFLY_TRY(make_tensor_map_2d(M(c.n_layers * 4 + 1), xn, T, h, h, p.bn));
+  BFLY_TRY(make_tensor_map_2d(M(c.n_layers * 4 + 2), attn_out, T, q_local * dh, q_local * dh, p.bn));
+  BFLY_TRY(make_tensor_map_2d(M(c.n_layers * 4 + 3), act, T, f_block, f_block, p.bn));
+  std::memcpy(p.map_head_param, M(c.n_layers * 4 + 0), 128);
+  std::memcpy(p.map_xg_param, M(c.n_layers * 4 + 1), 128);
+  char* d_maps = nullptr;
+  BFLY_TRY(dev_alloc(this, &d_maps, maps.size(), &workspace_bytes));
+  BFLY_CUDA(cudaMemcpy(d_maps, maps.data(), maps.size(), cudaMemcpyHostToDevice));
+  p.maps = d_maps;
+  std::vector<StepLayer> sl((size_t)c.n_layers);
+  for (int l = 0; l < c.n_layers; ++l)
+    sl[(size_t)l] = StepLayer{layers[l].attn_norm_w, layers[l].ffn_norm_w, kv_pages + (int64_t)l * layer_kv_elems};
+  StepLayer* d_layers = nullptr;
+  BFLY_TRY(dev_alloc(this, &d_layers, sl.size(), &workspace_bytes));
+  BFLY_CUDA(cudaMemcpy(d_layers, sl.data(), sl.size() * sizeof(StepLayer), cudaMemcpyHostToDevice));
+  p.layers = d_layers;
+  p.final_norm_w = final_norm_w;
+  p.residual = residual; p.xg = xn; p.q = q; p.attn_out = attn_out; p.act = act;
+  BFLY_TRY(dev_alloc(this, &p.ssq, (size_t)3 * T * p.chunks, &workspace_bytes));
+  BFLY_TRY(dev_alloc(this, &p.part_o, (size_t)T * q_local * p.attn_splits * dh, &workspace_bytes));
+  BFLY_TRY(dev_alloc(this, &p.part_ml, (size_t)T * q_local * p.attn_splits * 2, &workspace_bytes));
+  p.tokens = cur_tokens; p.embed = embed; p.history = history; p.step_counter = step_counter; p.keys = keys;
+  p.logits = want_logits ? logits : nullptr;
+  p.logits_ld = v_shard;
+  p.seq_lens = seq_lens; p.page_table = page_table; p.pages_per_seq = pages_per_seq; p.page_size = c.page_size;
+  p.rope_table = rope_table;
+  sp.n_counters = step_phase_count(c.n_layers, p.attn_splits);
+  BFLY_TRY(dev_alloc(this, &p.counters, (size_t)sp.n_counters, &workspace_bytes));
+  if (getenv("BFLY_STEP_TRACE")) {               // profiling: per-phase completion times of the last step
+    const size_t n_trace = (size_t)sp.n_counters + 2 + (size_t)sp.n_counters * sp.grid;
+    BFLY_TRY(dev_alloc(this, &p.trace, n_trace, &workspace_bytes));
+    BFLY_CUDA(cudaMemset(p.trace, 0, n_trace * sizeof(unsigned long long)));
+  }
+  p.peers = ar;
+  p.ar_step = ar_step;
+  p.ar_on = (c.tp > 1 && p2p_ready) ? 1 : 0;
+  BFLY_CUDA(cudaDeviceSynchronize());
+  step_plans[key] = sp;
+  *out = &step_plans[key];
+  return BFLY_OK;
+}
+
+// One decode step of B sequences as the fused kernel + the greedy-token exchange.
+int Engine::forward_step(int B, bool want_logits, bool record_history) {
+  StepPlan* sp = nullptr;
+  BFLY_TRY(build_step_plan(B, want_logits, &sp));
+  StepParams p = sp->p;
+  if (!record_history) p.history = nullptr;
+  BFLY_CUDA(cudaMemsetAsync(p.counters, 0, (size_t)sp->n_counters * sizeof(unsigned), stream));
+  BFLY_TRY(launch_decode_step(p, sp->grid, stream));
+  if (d.tp > 1) {
+    BFLY_TRY(all_gather_bytes(keys, keys_all, (size_t)d.max_batch * sizeof(unsigned long long)));
+    BFLY_TRY(launch_pick_tokens_pitched(keys_all, d.tp, d.max_batch, B, cur_tokens, stream));
+  } else {
+    BFLY_TRY(launch_pick_tokens_pitched(keys, 1, d.max_batch, B, cur_tokens, stream));
+  }
+  BFLY_TRY(launch_advance(seq_lens, B, 1, record_history ? step_counter : nullptr, p.ar_on ? ar_step : nullptr, stream));
+  return BFLY_OK;
+}
+
 int Engine::check_ready(int B) {
   if (!ready) { set_error("bfly_weights_ready() has not succeeded yet"); return BFLY_ESTATE; }
   BFLY_CHECK(B >= 1 && B <= d.max_batch, "batch must be in [1, max_batch]");
@@ -642,11 +804,15 @@ int Engine::decode_graph(int B, bool want_logits, GraphEntry** out) {
   const int key = B * 2 + (want_logits ? 1 : 0);
   auto it = graphs.find(key);
   if (it != graphs.end()) { *out = &it->second; return BFLY_OK; }
+  if (step_supported(B)) {                  // allocations and tensor maps happen before the capture begins
+    StepPlan* sp = nullptr;
+    BFLY_TRY(build_step_plan(B, want_logits, &sp));
+  }
   GraphEntry ge{};
   const unsigned long long before = t_launch_count;
   cudaGraph_t graph = nullptr;
   BFLY_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
-  const int rc = forward(cur_tokens, 0, B, 1, want_logits, true);
+  const int rc = step_supported(B) ? forward_step(B, want_logits, true) : forward(cur_tokens, 0, B, 1, want_logits, true);
   const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
   ge.kernel_nodes = (int)(t_launch_count - before);
   g_launch_count.fetch_sub((unsigned long long)ge.kernel_nodes, std::memory_order_relaxed);   // captured, not executed
@@ -721,6 +887,71 @@ int Engine::set_ar_mode(int mode) {
     graphs.clear();
   }
   ar_mode = mode;
+  return BFLY_OK;
+}
+
+// Microbenchmark of C1 (profiles/r02_c1_latency.txt): `iters` back-to-back calls of the fused all-reduce +
+// residual add + norm kernel on T rows (all ranks call this together), and of the plain add+norm kernel on
+// the same rows, timed with CUDA events on the ctx stream.  Average microseconds per call.
+int Engine::bench_allreduce(int T, int iters, float* us_allreduce, float* us_plain) {
+  BFLY_CHECK(p2p_ready, "bench_allreduce: needs tp > 1 with the peer-memory all-reduce initialised");
+  BFLY_CHECK(T >= 1 && T <= ar.max_rows && T <= d.max_tokens && iters >= 1 && us_allreduce && us_plain, "bench_allreduce: arguments");
+  BFLY_CUDA(cudaSetDevice(device));
+  const int h = d.hidden, calls = 2 * d.n_layers, ln = d.family == BFLY_FAMILY_GPT2;
+  const int two_shot = ar_mode >= 0 ? ar_mode : (d.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
+  BFLY_CUDA(cudaMemsetAsync(ws, 0, (size_t)T * h * sizeof(float), stream));
+  BFLY_CUDA(cudaMemsetAsync(residual, 0, (size_t)T * h * sizeof(float), stream));
+  cudaEvent_t e0, e1;
+  BFLY_CUDA(cudaEventCreate(&e0));
+  BFLY_CUDA(cudaEventCreate(&e1));
+  auto run = [&](int n, bool with_ar) -> int {
+    for (int i = 0; i < n; ++i) {
+      if (with_ar) {
+        BFLY_TRY(launch_ar_add_norm(residual, ws, 1, (int64_t)T * h, nullptr, final_norm_w, final_norm_b, d.norm_eps, ln, xn, T,
+                                    h, ar, i % calls, ar_step, calls, two_shot, stream));
+        if (i % calls == calls - 1) BFLY_TRY(launch_advance(seq_lens, 0, 0, nullptr, ar_step, stream));
+      } else {
+        BFLY_TRY(launch_add_norm(residual, ws, 1, (int64_t)T * h, nullptr, final_norm_w, final_norm_b, d.norm_eps, ln, xn, T, h,
+                                 stream));
+      }
+    }
+    return BFLY_OK;
+  };
+  const int n = ceil_div(iters, calls) * calls;          // whole epochs, so the step counter ends consistent
+  float ms = 0.f;
+  BFLY_TRY(run(calls, true));
+  BFLY_CUDA(cudaEventRecord(e0, stream));
+  BFLY_TRY(run(n, true));
+  BFLY_CUDA(cudaEventRecord(e1, stream));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  BFLY_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  *us_allreduce = ms * 1e3f / (float)n;
+  BFLY_TRY(run(calls, false));
+  BFLY_CUDA(cudaEventRecord(e0, stream));
+  BFLY_TRY(run(n, false));
+  BFLY_CUDA(cudaEventRecord(e1, stream));
+  BFLY_CUDA(cudaStreamSynchronize(stream));
+  BFLY_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  *us_plain = ms * 1e3f / (float)n;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return BFLY_OK;
+}
+
+// Profiling (BFLY_STEP_TRACE=1): nanosecond timestamps at which CTA 0 saw each phase of the LAST fused decode
+// step complete (entry 0 = kernel start); returns the number of entries, 0 when tracing is off.
+int Engine::read_step_trace(unsigned long long* out, int max_entries, int* n_out, int* splits_out) {
+  *n_out = 0;
+  for (auto& kv : step_plans) {
+    const StepPlan& sp = kv.second;
+    if (sp.p.trace == nullptr) continue;
+    const int n = std::min(max_entries, sp.n_counters + 2 + sp.n_counters * sp.grid);
+    BFLY_CUDA(cudaStreamSynchronize(stream));
+    BFLY_CUDA(cudaMemcpy(out, sp.p.trace, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    *n_out = n;
+    *splits_out = sp.p.attn_splits;
+    if (kv.first % 2 == 0) break;            // prefer the no-logits plan (the timed one)
+  }
   return BFLY_OK;
 }
 

@@ -7,6 +7,7 @@
 
 #include "../../include/butterfly_b200.h"
 #include "kernels.cuh"
+#include "decode_step.h"
 
 namespace bfly {
 
@@ -33,6 +34,12 @@ struct LayerW {
 struct GraphEntry {
   cudaGraphExec_t exec;
   int kernel_nodes;
+};
+
+// Device-side plan of the fused decode step kernel for one (batch, want_logits) pair.
+struct StepPlan {
+  StepParams p{};
+  int grid = 0, n_counters = 0;
 };
 
 struct Engine {
@@ -85,6 +92,12 @@ struct Engine {
   std::vector<void*> ipc_opened;
   int p2p_init();
   std::map<int, GraphEntry> graphs;       // key = B*2 + want_logits
+  bool fused_step = true;                 // decode runs as ONE persistent kernel per step where the model allows it
+  std::map<int, StepPlan> step_plans;     // same key
+  bool step_supported(int B) const;
+  int build_step_plan(int B, bool want_logits, StepPlan** out);
+  int forward_step(int B, bool want_logits, bool record_history);
+  int read_step_trace(unsigned long long* out, int max_entries, int* n_out, int* splits_out);
   int last_graph_nodes = 0;
 
   static int create(const bfly_model_desc& desc, int device, Engine** out);
@@ -99,6 +112,7 @@ struct Engine {
   int comm_init(const void* id128, int world, int rank);
   int set_page_table(const int32_t* table_host, int n_seqs, int pps);
   int set_ar_mode(int mode);
+  int bench_allreduce(int T, int iters, float* us_allreduce, float* us_plain);
 
   int prefill(const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);
   int prefill_at(int seq0, const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);

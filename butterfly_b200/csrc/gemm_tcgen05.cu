@@ -21,6 +21,7 @@
 #include <cstdlib>
 #include <mutex>
 
+#include "decode_step.h"
 #include "tcgen05_common.cuh"
 
 namespace bfly {
@@ -547,6 +548,11 @@ int make_map(CUtensorMap* map, const bf16* ptr, int64_t rows, int cols, int64_t 
 }
 
 }  // namespace
+
+int make_tensor_map_2d(void* out128, const bf16* ptr, int64_t rows, int cols, int64_t pitch, int box_rows) {
+  BFLY_TRY(gemm_init());
+  return make_map(reinterpret_cast<CUtensorMap*>(out128), ptr, rows, cols, pitch, box_rows);
+}
 
 int gemm_init() {
   std::call_once(g_init_once, [] {

@@ -75,6 +75,7 @@ constexpr int kMaxPeers = 8;
 struct ArPeers {
   float* recv[kMaxPeers];        // rank r's receive buffer [2 parities][tp][max_rows][h] fp32 (peer-mapped)
   unsigned* flags[kMaxPeers];    // rank r's epoch flags    [2 parities][tp][max_rows]
+  unsigned* cflags[kMaxPeers];   // rank r's per-chunk flags [2 parities][tp][max_rows][8] (fused decode step kernel)
   int tp, rank, max_rows;
 };
 int launch_ar_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,

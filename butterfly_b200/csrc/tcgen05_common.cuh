@@ -19,6 +19,8 @@ constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;   // L2 policy: stream (
 constexpr uint64_t kEvictLast = 0x14F0000000000000ull;    // L2 policy: keep (activations)
 
 // ---- PTX wrappers ---------------------------------------------------------------------------
+#ifndef BFLY_MBAR_HELPERS      // attn_common.cuh defines the same helpers
+#define BFLY_MBAR_HELPERS
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -44,6 +46,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (clock64() - t0 > 4000000000ll) __trap();
   }
 }
+#endif  // BFLY_MBAR_HELPERS
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
                                             uint64_t policy) {
   asm volatile(

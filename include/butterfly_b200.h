@@ -92,6 +92,11 @@ int bfly_comm_init(bfly_ctx* ctx, const void* id128, int world, int rank);
  * are bit-identical.  Call it at a quiescent point with the SAME value on every rank. */
 int bfly_set_ar_mode(bfly_ctx* ctx, int mode);
 
+/* Latency of the decode all-reduce in isolation (tp > 1, every rank calls it together): average microseconds per
+ * call of the fused all-reduce + residual add + norm kernel over `iters` back-to-back calls on T rows of the
+ * model's hidden size, and of the plain add + norm kernel on the same rows (the difference is the exchange). */
+int bfly_bench_allreduce(bfly_ctx* ctx, int T, int iters, float* us_allreduce, float* us_plain);
+
 /* ---- forward ------------------------------------------------------------------------------- */
 /* Optional: install a page table int32[n_seqs][pages_per_seq] (default: sequence b owns pages
  * b*pages_per_seq ...).  Physical page ids must be unique and < max_batch*pages_per_seq. */
@@ -118,6 +123,10 @@ int bfly_decode_enqueue(bfly_ctx* ctx, int B, int n_steps);
 /* The tokens fed at the n_steps steps of the LAST bfly_decode_enqueue / bfly_decode_greedy of B sequences
  * (int32[B][n_steps]); synchronises the ctx stream. */
 int bfly_read_history(bfly_ctx* ctx, int B, int n_steps, int32_t* tokens_out_host);
+/* Profiling of the fused decode step (contexts created with BFLY_STEP_TRACE=1 in the environment): the
+ * nanosecond timestamps at which CTA 0 saw each phase of the last step complete (entry 0 = kernel start, phase
+ * order as in csrc/decode_step.cu); *n_entries = 0 when tracing is off. */
+int bfly_read_step_trace(bfly_ctx* ctx, uint64_t* out_ns, int max_entries, int* n_entries, int* attn_splits);
 int bfly_sync(bfly_ctx* ctx);
 void* bfly_stream(bfly_ctx* ctx);        /* the ctx's cudaStream_t, for event timing by the caller */
 

@@ -11,7 +11,7 @@ import torch
 
 from butterfly_b200 import (GPT2_SMALL, LLAMA3_8B, LLAMA3_70B, MIXTRAL_8X7B, SyntheticSource, make_plan, shard_weights, synthetic_tokens, tiny)
 from oracle import OracleModel, ops
-from parity_gates import LOGIT_TOL, Gate
+from parity_gates import LOGIT_TOL, Gate, gates_for
 
 pytestmark = pytest.mark.gpu
 
@@ -38,8 +38,12 @@ def _run_parity(cfg, B, S, n_steps, device_synth, max_ctx=None, page_table=None,
         gm.set_page_table(page_table)
     toks = synthetic_tokens(cfg, B, S)
     lo, lg = om.prefill(toks), gm.prefill(toks)
-    gate, flips, close_calls = Gate(), [], 0
+    gate, flips, close_calls = Gate(cfg.n_layers), [], 0
     gate.add(lg, lo)
+    # a greedy flip can only be blamed on the kernels where the oracle's own top-1/top-2 margin exceeds twice the
+    # logit gate of this depth (closer calls are coin flips for any bf16 pipeline)
+    abs_gate, rel_max, _ = gates_for(cfg.n_layers)
+    clear = 2 * (abs_gate if abs_gate is not None else rel_max * lo.std().item())
     teacher, margins = [], []
     for step in range(n_steps):
         want_tok, got_tok = ops.argmax(lo), ops.argmax(lg)
@@ -49,7 +53,7 @@ def _run_parity(cfg, B, S, n_steps, device_synth, max_ctx=None, page_table=None,
         for b in range(B):
             if int(want_tok[b]) != int(got_tok[b]):
                 flips.append((step, b, float(margin[b])))
-            close_calls += int(margin[b] <= 2 * LOGIT_TOL)
+            close_calls += int(margin[b] <= clear)
         assert torch.equal(gm.last_tokens, got_tok), "engine greedy token != argmax of its own logits"
         lo, lg = om.decode(want_tok), gm.decode(want_tok)          # teacher-forced with the oracle's token
         gate.add(lg, lo)
@@ -64,13 +68,13 @@ def _run_parity(cfg, B, S, n_steps, device_synth, max_ctx=None, page_table=None,
         for s, b, m in sorted(mism):
             first.setdefault(b, (s, b, m))
         free_report = f" free-running agreement={(fed == want).float().mean().item():.3f} first divergences={sorted(first.values())}"
-        bad_free = [f for f in first.values() if f[2] > 2 * LOGIT_TOL]
+        bad_free = [f for f in first.values() if f[2] > clear]
         assert not bad_free, f"free-running greedy diverged where the oracle's margin is clear: {bad_free}"
     gm.close()
     print(f"\n[{cfg.name}] L={cfg.n_layers} B={B} S={S} steps={n_steps}: {gate.summary()} "
-          f"close_calls={close_calls} flips={flips}{free_report}")
+          f"close_calls(margin<={clear:.3f})={close_calls}/{B * n_steps} flips={flips}{free_report}")
     gate.check(cfg.name)
-    bad = [f for f in flips if f[2] > 2 * LOGIT_TOL]
+    bad = [f for f in flips if f[2] > clear]
     assert not bad, f"greedy token mismatch at positions with a clear oracle margin: {bad}"
     return gate.max_abs
 

@@ -68,7 +68,7 @@ def _run(cfg, world, B, S, steps, tmp_path, ar_modes=(AR_AUTO,), alternate=False
              nprocs=world, join=True)
     results = [torch.load(f"{out}.{r}") for r in range(world)]
     for mode in ar_modes:
-        gate = Gate()
+        gate = Gate(cfg.n_layers)
         for r, per_mode in enumerate(results):
             res = per_mode[mode]
             gate.add(res["prefill"], want_prefill)
