@@ -180,6 +180,7 @@ __device__ __forceinline__ void gemm_phase(const StepParams& P, const StepGemm& 
   const int stages = P.stages, bn = P.bn;
   const uint32_t b_bytes = (uint32_t)bn * BK * 2;
   const uint32_t stage_bytes = kABytes + b_bytes;
+  const int chains = (P.tune & 32) ? 4 : ((P.tune & 16) ? 2 : 1);
   const uint64_t pol_w = (P.tune & 1) ? 0x1000000000000000ull : kEvictFirst;     // evict_normal vs evict_first
 
   if (warp < kProducerWarps) {
@@ -235,7 +236,8 @@ __device__ __forceinline__ void gemm_phase(const StepParams& P, const StepGemm& 
         tcgen05_fence_after();
         const uint64_t da = umma_smem_desc(sm.ring + (uint32_t)s * stage_bytes);
         const uint64_t db = umma_smem_desc(sm.ring + (uint32_t)s * stage_bytes + kABytes);
-        const uint32_t d_tmem = tmem_base + acc * (uint32_t)bn;
+        // independent accumulation chains: consecutive MMAs do not wait on each other's accumulator
+        const uint32_t d_tmem = tmem_base + acc * (uint32_t)(bn * chains);
         if (P.tune & 8) {                           // timing experiment: no MMAs, the stage is handed straight back
           asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(sm.empty + 8u * s) : "memory");
           if (seg_last) {
@@ -246,7 +248,8 @@ __device__ __forceinline__ void gemm_phase(const StepParams& P, const StepGemm& 
         }
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k)
-          umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)(!seg_first || k != 0));
+          umma_bf16(d_tmem + (uint32_t)((k & (chains - 1)) * bn), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                    (uint32_t)(!seg_first || k >= chains));
         umma_commit(sm.empty + 8u * s);
         if (seg_last) {
           umma_commit(sm.tfull + 8u * acc);
@@ -266,7 +269,7 @@ __device__ __forceinline__ void gemm_phase(const StepParams& P, const StepGemm& 
       const uint32_t acc = acc_it & 1u;
       mbar_wait(sm.tfull + 8u * acc, (acc_it >> 1) & 1u);
       tcgen05_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (uint32_t)bn;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (uint32_t)(bn * chains);
       const int m = tile * BM + ml;
       float* dst = g.out + ((int64_t)slice * P.T) * g.M + m;
       for (int c0 = 0; c0 < bn; c0 += 16) {
@@ -274,6 +277,13 @@ __device__ __forceinline__ void gemm_phase(const StepParams& P, const StepGemm& 
         uint32_t r[16];
         tmem_ld16(taddr + (uint32_t)c0, r);
         tmem_ld_wait();
+        for (int ch = 1; ch < chains; ++ch) {       // fold the accumulation chains in chain order
+          uint32_t r2[16];
+          tmem_ld16(taddr + (uint32_t)(ch * bn + c0), r2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+        }
         if (m < g.M) {
 #pragma unroll
           for (int j = 0; j < 16; ++j)
@@ -305,7 +315,7 @@ __device__ __forceinline__ void norm_phase(const StepParams& P, const StepGemm* 
   unsigned epoch = 0;
   int parity = 0;
   if (ar) {
-    epoch = (*P.ar_step) * (unsigned)(2 * P.n_layers) + (unsigned)ar_call + 1u;
+    epoch = __ldcg(P.ar_step) * (unsigned)(2 * P.n_layers) + (unsigned)ar_call + 1u;
     parity = ar_call & 1;
   }
   for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
@@ -774,7 +784,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kProducerWarps) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sm.tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sm.tmem_slot), "r"(512u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   if (warp == 0 && lane == 0) {
@@ -862,7 +872,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const __gr
   tcgen05_fence_before();
   __syncthreads();
   if (warp == kProducerWarps)
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
 }
 
 constexpr size_t kStepSmem = 1024 + kStepRingBytes + 8 * (2 * kRingStages + 4 + kAW * kAStages) + 64;

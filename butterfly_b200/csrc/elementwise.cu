@@ -479,7 +479,7 @@ __global__ void advance_kernel(int* seq_lens, int B, int S, int* step_counter, u
 }
 
 int launch_advance(int* seq_lens, int B, int S, int* step_counter, unsigned* ar_step, cudaStream_t stream) {
-  BFLY_CUDA(launch_pdl(advance_kernel, dim3(ceil_div(B, 128)), dim3(128), 0, stream, seq_lens, B, S, step_counter, ar_step));
+  BFLY_CUDA(launch_pdl(advance_kernel, dim3(std::max(1, ceil_div(B, 128))), dim3(128), 0, stream, seq_lens, B, S, step_counter, ar_step));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;

@@ -141,6 +141,17 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     // path so far, so it is opt-in: BFLY_FUSED_STEP=1.
     env = getenv("BFLY_FUSED_STEP");
     e->fused_step = env && env[0] == '1';
+    env = getenv("BFLY_AR_CLUSTER");                    // A/B knob: 0 = one CTA per row (round-1 kernel)
+    // (rows split over a cluster of CTAs measured SLOWER than one CTA per row at tp=2 and tp=8 -- more flags in
+    //  flight, cluster launch cost -- so it is off unless asked for: "a" = automatic chunk count, "1".."8" = that many)
+    e->ar_chunks = 0;
+    if (env && env[0] == 'a') e->ar_chunks = ar_chunks_for(c.hidden);
+    if (env && env[0] >= '1' && env[0] <= '8' && c.hidden % ((env[0] - '0') * 4) == 0) e->ar_chunks = env[0] - '0';
+    env = getenv("BFLY_AR_BF16");                       // A/B knob: partial sums cross NVLink as bf16
+    e->ar_bf16 = (env && env[0] == '1' && e->ar_chunks > 0) ? 1 : 0;
+    env = getenv("BFLY_AR_PROTO");                      // "flags" = round-1 epoch-flag protocol; default: flag-free (Lamport)
+    e->ar_lamport = (env && env[0] == 'f') ? 0 : 1;
+    if (e->fused_step || e->ar_chunks > 0) e->ar_lamport = 0;     // those kernels speak the flag protocol
     env = getenv("BFLY_AR_TWO_SHOT");                   // initial all-reduce mode; bfly_set_ar_mode() changes it
     e->ar_mode = env ? (env[0] == '1' ? 1 : 0) : -1;
   }
@@ -362,6 +373,10 @@ int Engine::p2p_init() {
   char* base = nullptr;
   BFLY_TRY(dev_alloc(this, &base, flags_bytes + recv_bytes, &workspace_bytes));
   BFLY_CUDA(cudaMemset(base, 0, flags_bytes + recv_bytes));
+  if (ar_lamport) {
+    BFLY_TRY(ar_fill_sentinel(reinterpret_cast<float*>(base + flags_bytes), recv_bytes / sizeof(float), stream));
+    BFLY_CUDA(cudaStreamSynchronize(stream));
+  }
   BFLY_TRY(dev_alloc(this, &ar_step, 1, &workspace_bytes));
   BFLY_CUDA(cudaMemset(ar_step, 0, sizeof(unsigned)));
   cudaIpcMemHandle_t mine;
@@ -504,7 +519,7 @@ int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call,
     // every rank takes the same branch: T, h, tp and the mode are identical across the group
     const int two_shot = ar_mode >= 0 ? ar_mode : (d.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
     return launch_ar_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, ar, idx,
-                              ar_step, 2 * d.n_layers, two_shot, stream);
+                              ar_step, 2 * d.n_layers, two_shot, ar_chunks, ar_bf16, ar_lamport, stream);
   }
   return launch_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, stream);
 }
@@ -908,7 +923,7 @@ int Engine::bench_allreduce(int T, int iters, float* us_allreduce, float* us_pla
     for (int i = 0; i < n; ++i) {
       if (with_ar) {
         BFLY_TRY(launch_ar_add_norm(residual, ws, 1, (int64_t)T * h, nullptr, final_norm_w, final_norm_b, d.norm_eps, ln, xn, T,
-                                    h, ar, i % calls, ar_step, calls, two_shot, stream));
+                                    h, ar, i % calls, ar_step, calls, two_shot, ar_chunks, ar_bf16, ar_lamport, stream));
         if (i % calls == calls - 1) BFLY_TRY(launch_advance(seq_lens, 0, 0, nullptr, ar_step, stream));
       } else {
         BFLY_TRY(launch_add_norm(residual, ws, 1, (int64_t)T * h, nullptr, final_norm_w, final_norm_b, d.norm_eps, ln, xn, T, h,

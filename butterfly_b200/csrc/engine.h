@@ -89,6 +89,8 @@ struct Engine {
   bool p2p_ready = false;
   unsigned* ar_step = nullptr;
   int ar_mode = -1;                       // -1 by size, 0 one-shot, 1 two-shot (set_ar_mode)
+  int ar_lamport = 1;                     // flag-free decode all-reduce protocol (allreduce_norm.cu)
+  int ar_chunks = 0, ar_bf16 = 0;         // cluster CTAs per row of the fused all-reduce (0 = one CTA per row); bf16 payload
   std::vector<void*> ipc_opened;
   int p2p_init();
   std::map<int, GraphEntry> graphs;       // key = B*2 + want_logits

@@ -81,7 +81,12 @@ struct ArPeers {
 int launch_ar_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
                        const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
                        int T, int h, const ArPeers& peers, int call_idx, const unsigned* step_ptr, int calls_per_step,
-                       int two_shot, cudaStream_t stream);
+                       int two_shot, int chunks, int bf16_payload, int lamport, cudaStream_t stream);
+// lamport = 1: flag-free protocol (self-validating words, sentinel -0.0f); one CTA per row, fp32 payload.
+int ar_fill_sentinel(float* recv, size_t n_floats, cudaStream_t stream);
+// chunks: 0 = one CTA per row; C >= 1 = each row split over a cluster of C CTAs (ar_chunks_for picks C from h).
+// bf16_payload (cluster variant only): partial sums cross NVLink as bf16.
+int ar_chunks_for(int h);
 
 // attn_decode.cu -- paged-KV attention, one query token per (virtual) sequence, split over the context
 int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count);
