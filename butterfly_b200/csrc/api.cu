@@ -269,6 +269,17 @@ int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int3
   });
 }
 
+int bfly_k_attn_decode_rope(const float* qkv, int n_partials, int64_t partial_stride, const void* bias_bf16,
+                            const float* rope_table, void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
+                            int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int T, int nq, float* part_o,
+                            float* part_ml, int n_splits, void* out_bf16, void* stream) {
+  return guarded(nullptr, [&]() -> int {
+    KvLayout kv{mb(kv_pages_bf16), page_table, pages_per_seq, page_size, kv_local, head_dim};
+    return launch_attn_decode_fused(qkv, n_partials, partial_stride, cb(bias_bf16), reinterpret_cast<const float2*>(rope_table),
+                                    kv, seq_lens, T, nq, part_o, part_ml, n_splits, mb(out_bf16), as_stream(stream));
+  });
+}
+
 int bfly_k_attn_decode_splits(int T, int kv_local, int max_ctx) {
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) {

@@ -33,14 +33,27 @@ constexpr size_t attn_smem_bytes() {
   return (size_t)kWarps * kStages * 2 * kTile * D * 2      // K + V^T rings
          + (size_t)kWarps * 8 * D * 4                      // per-warp O^T for the merge
          + (size_t)kWarps * 8 * 2 * 4                      // per-warp (m, l)
-         + (size_t)kWarps * kStages * 8 + 128;             // mbarriers + alignment slack
+         + (size_t)kWarps * kStages * 8 + 128              // mbarriers + alignment slack
+         + (size_t)8 * D * 2;                              // fused variant: rotated q of the GQA group (bf16)
 }
 
-template <int D, int G>
+// Fused variant (kFused, decode only: S == 1): the kernel also does what rope_kv_kernel did -- it folds the QKV
+// GEMM's split-K slices (+bias) for its own query heads, rotates them (RoPE) and keeps them in shared memory, and
+// the CTA that owns the tile of the NEW token folds/rotates that token's K and V row, appends it to the paged
+// cache and only then fetches that tile.  One kernel and one dependency less per layer.
+struct FusedQkv {
+  const float* qkv;          // fp32 [n_partials][T][(nq + 2 nk) * D] slices of the QKV projection
+  int n_partials;
+  int64_t partial_stride;
+  const bf16* bias;          // [(nq + 2 nk) * D] or nullptr
+  const float2* rope_table;  // [pos][D/2] (cos, sin) or nullptr (learned positions)
+};
+
+template <int D, int G, bool kFused>
 __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
     const bf16* __restrict__ q, KvLayout kv, const int* __restrict__ seq_lens, int S, int nq,
     float* __restrict__ part_o, float* __restrict__ part_ml, int n_splits, float scale_log2,
-    bf16* __restrict__ out_direct) {
+    bf16* __restrict__ out_direct, FusedQkv fq) {
   static_assert(G >= 1 && G <= 8 && (D == 32 || D == 64 || D == 128), "unsupported shape");
   constexpr int KSTEP_PAIRS = D / 32;         // 16-byte chunks per thread per K row = pairs of k-steps
   constexpr int MT_O = D / 16;                // m-tiles of O^T
@@ -103,6 +116,73 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
       for (int i = 0; i < n_pre; ++i)
         if (tile_begin + warp + i * kWarps != last_tile) issue(i);
     pdl_wait();                                        // q and the new K/V rows are ready from here on
+    if constexpr (kFused) {
+      // ---- what rope_kv_kernel did, for this CTA's heads only (S == 1: token t sits at position ctx - 1) ----
+      bf16* sm_q = reinterpret_cast<bf16*>(smem + attn_smem_bytes<D>() - (size_t)8 * D * 2);
+      constexpr int half = D / 2;
+      const int nk = kv.kv_local, pos = ctx - 1;
+      const int ld = (nq + 2 * nk) * D;
+      const float* row = fq.qkv + (int64_t)t * ld;
+      auto fold_pair = [&](int c0, float& x0, float& x1) {        // columns c0 and c0 + half, slices in index order
+        x0 = 0.f; x1 = 0.f;
+        int p = 0;
+        for (; p + 4 <= fq.n_partials; p += 4) {
+          float a[4], b[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            a[k] = row[(p + k) * fq.partial_stride + c0];
+            b[k] = row[(p + k) * fq.partial_stride + c0 + half];
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { x0 += a[k]; x1 += b[k]; }
+        }
+        for (; p < fq.n_partials; ++p) {
+          x0 += row[p * fq.partial_stride + c0];
+          x1 += row[p * fq.partial_stride + c0 + half];
+        }
+        if (fq.bias != nullptr) {
+          x0 += __bfloat162float(fq.bias[c0]);
+          x1 += __bfloat162float(fq.bias[c0 + half]);
+        }
+      };
+      auto rotate = [&](int i, float& x0, float& x1) {
+        if (fq.rope_table != nullptr) {
+          const float2 cs = fq.rope_table[(int64_t)pos * half + i];
+          const float y0 = x0 * cs.x - x1 * cs.y, y1 = x1 * cs.x + x0 * cs.y;
+          x0 = y0; x1 = y1;
+        }
+      };
+      for (int idx = threadIdx.x; idx < G * half; idx += kWarps * 32) {
+        const int g = idx / half, i = idx - g * half;
+        float x0, x1;
+        fold_pair((kvh * G + g) * D + i, x0, x1);
+        rotate(i, x0, x1);
+        sm_q[g * D + i] = __float2bfloat16_rn(x0);
+        sm_q[g * D + i + half] = __float2bfloat16_rn(x1);
+      }
+      const bool owns_new = last_tile >= tile_begin && last_tile < tile_end;      // CTA-uniform
+      if (owns_new) {
+        const int page = table[pos / ps];
+        const int slot = pos % ps;
+        bf16* kblk = kv.base + (int64_t)page * page_stride + (int64_t)kvh * head_stride;
+        bf16* vblk = kblk + (int64_t)kv.kv_local * head_stride;
+        for (int idx = threadIdx.x; idx < 2 * half; idx += kWarps * 32) {
+          const int which = idx / half, i = idx - which * half;              // 0: K pair (rotated), 1: V pair
+          float x0, x1;
+          fold_pair((nq + which * nk + kvh) * D + i, x0, x1);
+          if (which == 0) {
+            rotate(i, x0, x1);
+            kblk[kv_k_offset(slot, i, D)] = __float2bfloat16_rn(x0);
+            kblk[kv_k_offset(slot, i + half, D)] = __float2bfloat16_rn(x1);
+          } else {
+            vblk[kv_v_offset(slot, i, D)] = __float2bfloat16_rn(x0);
+            vblk[kv_v_offset(slot, i + half, D)] = __float2bfloat16_rn(x1);
+          }
+        }
+        asm volatile("fence.proxy.async;" ::: "memory");     // the bulk copy below (async proxy) must see these rows
+      }
+      __syncthreads();
+    }
     if (lane == 0)
       for (int i = 0; i < n_pre; ++i)
         if (S != 1 || tile_begin + warp + i * kWarps == last_tile) issue(i);
@@ -113,7 +193,12 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_decode_kernel(
 #pragma unroll
   for (int j = 0; j < KSTEP_PAIRS; ++j) {
     uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (r < G) v = *reinterpret_cast<const uint4*>(q + ((int64_t)t * nq + kvh * G + r) * D + c * 8 + 32 * j);
+    if constexpr (kFused) {
+      const bf16* sm_q = reinterpret_cast<const bf16*>(smem + attn_smem_bytes<D>() - (size_t)8 * D * 2);
+      if (r < G) v = *reinterpret_cast<const uint4*>(sm_q + r * D + c * 8 + 32 * j);
+    } else {
+      if (r < G) v = *reinterpret_cast<const uint4*>(q + ((int64_t)t * nq + kvh * G + r) * D + c * 8 + 32 * j);
+    }
     qb[j][0] = v.x; qb[j][1] = v.y; qb[j][2] = v.z; qb[j][3] = v.w;
   }
 
@@ -263,25 +348,43 @@ __global__ void attn_combine_kernel(const float* __restrict__ part_o, const floa
   out[th * D + dd] = __float2bfloat16_rn(O / L);
 }
 
-template <int D, int G>
+template <int D, int G, bool kFused>
 int launch_impl(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, int T, int nq, float* part_o,
-                float* part_ml, int n_splits, bf16* out, cudaStream_t stream) {
+                float* part_ml, int n_splits, bf16* out, const FusedQkv& fq, cudaStream_t stream) {
   static PerDeviceOnce attr;
   constexpr size_t smem = attn_smem_bytes<D>();
   BFLY_TRY(attr.run([] {
-    BFLY_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BFLY_CUDA(cudaFuncSetAttribute(attn_decode_kernel<D, G, kFused>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     return (int)BFLY_OK;
   }));
   dim3 grid(n_splits, kv.kv_local, T);
   const float scale_log2 = 1.4426950408889634f / sqrtf((float)D);
-  BFLY_CUDA(launch_pdl(attn_decode_kernel<D, G>, grid, dim3(kWarps * 32), smem, stream, q, kv, seq_lens, S, nq, part_o,
-                       part_ml, n_splits, scale_log2, n_splits == 1 ? out : nullptr));
+  BFLY_CUDA(launch_pdl(attn_decode_kernel<D, G, kFused>, grid, dim3(kWarps * 32), smem, stream, q, kv, seq_lens, S, nq, part_o,
+                       part_ml, n_splits, scale_log2, n_splits == 1 ? out : nullptr, fq));
   count_launch();
   if (n_splits > 1) {
     BFLY_CUDA(launch_pdl(attn_combine_kernel<D>, dim3(T * nq), dim3(D), 0, stream, part_o, part_ml, n_splits, out));
     count_launch();
   }
   return BFLY_OK;
+}
+
+template <bool kFused>
+int dispatch(const bf16* q, const KvLayout& kv, const int* seq_lens, int S, int T, int nq, float* part_o, float* part_ml,
+             int n_splits, bf16* out, const FusedQkv& fq, cudaStream_t stream) {
+  BFLY_CHECK(T > 0 && T <= 65535 && n_splits >= 1 && kv.kv_local >= 1 && nq % kv.kv_local == 0,
+             "attn_decode: bad shape (T<=65535, nq % kv_local == 0)");
+  BFLY_CHECK(kv.page_size % kTile == 0, "attn_decode: page_size must be a multiple of 32");
+  const int G = nq / kv.kv_local, D = kv.head_dim;
+#define BFLY_ATTN_CASE(DD, GG) \
+  if (D == DD && G == GG) return launch_impl<DD, GG, kFused>(q, kv, seq_lens, S, T, nq, part_o, part_ml, n_splits, out, fq, stream)
+  BFLY_ATTN_CASE(128, 1); BFLY_ATTN_CASE(128, 2); BFLY_ATTN_CASE(128, 4); BFLY_ATTN_CASE(128, 8);
+  BFLY_ATTN_CASE(64, 1);  BFLY_ATTN_CASE(64, 2);  BFLY_ATTN_CASE(64, 4);  BFLY_ATTN_CASE(64, 8);
+  BFLY_ATTN_CASE(32, 1);  BFLY_ATTN_CASE(32, 2);  BFLY_ATTN_CASE(32, 4);  BFLY_ATTN_CASE(32, 8);
+#undef BFLY_ATTN_CASE
+  set_error("attn_decode: unsupported (head_dim, q-per-kv) = (" + std::to_string(D) + ", " + std::to_string(G) +
+            "); supported head_dim {32,64,128}, group {1,2,4,8}");
+  return BFLY_EINVAL;
 }
 
 }  // namespace
@@ -302,19 +405,17 @@ int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count) {
 
 int launch_attn_decode(const bf16* q, KvLayout kv, const int* seq_lens, int S, int T, int nq, float* part_o,
                        float* part_ml, int n_splits, bf16* out, cudaStream_t stream) {
-  BFLY_CHECK(T > 0 && T <= 65535 && n_splits >= 1 && kv.kv_local >= 1 && nq % kv.kv_local == 0,
-             "attn_decode: bad shape (T<=65535, nq % kv_local == 0)");
-  BFLY_CHECK(kv.page_size % kTile == 0, "attn_decode: page_size must be a multiple of 32");
-  const int G = nq / kv.kv_local, D = kv.head_dim;
-#define BFLY_ATTN_CASE(DD, GG) \
-  if (D == DD && G == GG) return launch_impl<DD, GG>(q, kv, seq_lens, S, T, nq, part_o, part_ml, n_splits, out, stream)
-  BFLY_ATTN_CASE(128, 1); BFLY_ATTN_CASE(128, 2); BFLY_ATTN_CASE(128, 4); BFLY_ATTN_CASE(128, 8);
-  BFLY_ATTN_CASE(64, 1);  BFLY_ATTN_CASE(64, 2);  BFLY_ATTN_CASE(64, 4);  BFLY_ATTN_CASE(64, 8);
-  BFLY_ATTN_CASE(32, 1);  BFLY_ATTN_CASE(32, 2);  BFLY_ATTN_CASE(32, 4);  BFLY_ATTN_CASE(32, 8);
-#undef BFLY_ATTN_CASE
-  set_error("attn_decode: unsupported (head_dim, q-per-kv) = (" + std::to_string(D) + ", " + std::to_string(G) +
-            "); supported head_dim {32,64,128}, group {1,2,4,8}");
-  return BFLY_EINVAL;
+  return dispatch<false>(q, kv, seq_lens, S, T, nq, part_o, part_ml, n_splits, out, FusedQkv{}, stream);
+}
+
+// Decode step (one new token per sequence): RoPE + KV append + attention in one kernel, straight from the QKV
+// projection's fp32 slices.
+int launch_attn_decode_fused(const float* qkv, int n_partials, int64_t partial_stride, const bf16* bias,
+                             const float2* rope_table, KvLayout kv, const int* seq_lens, int T, int nq, float* part_o,
+                             float* part_ml, int n_splits, bf16* out, cudaStream_t stream) {
+  BFLY_CHECK(qkv != nullptr && n_partials >= 1, "attn_decode_fused: qkv slices missing");
+  FusedQkv fq{qkv, n_partials, partial_stride, bias, rope_table};
+  return dispatch<true>(nullptr, kv, seq_lens, 1, T, nq, part_o, part_ml, n_splits, out, fq, stream);
 }
 
 }  // namespace bfly

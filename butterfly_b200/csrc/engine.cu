@@ -141,6 +141,11 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     // path so far, so it is opt-in: BFLY_FUSED_STEP=1.
     env = getenv("BFLY_FUSED_STEP");
     e->fused_step = env && env[0] == '1';
+    // RoPE + KV append inside the decode attention kernel (one kernel less per layer) measured SLOWER than the
+    // separate rope_kv kernel under programmatic dependent launch (tp=1 4.85 vs 4.77 ms/step, tp=8 shard 1.74 vs
+    // 1.70): the fold sits on the attention kernel's critical path instead of overlapping its KV prefetch.  Opt-in.
+    env = getenv("BFLY_FUSED_ROPE");
+    e->fused_rope = env && env[0] == '1';
     env = getenv("BFLY_AR_CLUSTER");                    // A/B knob: 0 = one CTA per row (round-1 kernel)
     // (rows split over a cluster of CTAs measured SLOWER than one CTA per row at tp=2 and tp=8 -- more flags in
     //  flight, cluster launch cost -- so it is off unless asked for: "a" = automatic chunk count, "1".."8" = that many)
@@ -545,11 +550,20 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
     int s = 1;
     BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, w.attn_norm_w, w.attn_norm_b));
     BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s));
-    BFLY_TRY(launch_rope_kv(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, lens, S, T, q_local, kv_local, q, kv,
-                            stream));
+    const bool fuse_rope = S == 1 && fused_rope;
+    if (!fuse_rope)
+      BFLY_TRY(launch_rope_kv(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, lens, S, T, q_local, kv_local, q, kv,
+                              stream));
     if (S > 1)
       BFLY_TRY(launch_attn_prefill(q, kv, lens, S, nb, q_local, attn_out, stream));
-    else {
+    else if (fuse_rope) {
+      if ((size_t)T * q_local * attn_splits * dh > part_o_elems || (size_t)T * q_local * attn_splits * 2 > part_ml_elems) {
+        set_error("split-attention scratch too small (internal sizing error)");
+        return BFLY_ESTATE;
+      }
+      BFLY_TRY(launch_attn_decode_fused(ws, s, (int64_t)T * qkv_rows, w.bqkv, rope_table, kv, lens, T, q_local, part_o,
+                                        part_ml, attn_splits, attn_out, stream));
+    } else {
       if ((size_t)T * q_local * attn_splits * dh > part_o_elems || (size_t)T * q_local * attn_splits * 2 > part_ml_elems) {
         set_error("split-attention scratch too small (internal sizing error)");
         return BFLY_ESTATE;

@@ -53,6 +53,7 @@ struct Engine {
   int n_blocks = 1, f_block = 0, ffn_in_rows = 0, ffn_act_cols = 0;
   bool gated = true;
   bool fused_swiglu = true;                // gate/up GEMM applies the SwiGLU in its epilogue
+  bool fused_rope = false;                 // decode attention folds the QKV slices, RoPE and the KV append itself
   bool moe_grouped = true;                 // MoE prefill runs each expert over its routed tokens only
   int moe_rows_cap = 0;                    // max_tokens * min(top_k, experts_local)
   int *moe_cnt = nullptr, *moe_off = nullptr, *moe_idx = nullptr;

@@ -93,6 +93,12 @@ int attn_decode_splits(int T, int kv_local, int max_ctx, int sm_count);
 int launch_attn_decode(const bf16* q, KvLayout kv, const int* seq_lens, int S, int T, int nq, float* part_o,
                        float* part_ml, int n_splits, bf16* out, cudaStream_t stream);
 
+// decode only (S == 1): the same attention with the RoPE / KV-append step folded in -- reads the QKV projection's
+// fp32 slices [n_partials][T][(nq + 2 kv_local) * head_dim] (+bias), appends the new K/V row to the cache itself
+int launch_attn_decode_fused(const float* qkv, int n_partials, int64_t partial_stride, const bf16* bias,
+                             const float2* rope_table, KvLayout kv, const int* seq_lens, int T, int nq, float* part_o,
+                             float* part_ml, int n_splits, bf16* out, cudaStream_t stream);
+
 // attn_prefill.cu -- causal attention of S new tokens per sequence over the paged cache (tensor cores)
 int launch_attn_prefill(const bf16* q, KvLayout kv, const int* seq_lens, int S, int B, int nq, bf16* out,
                         cudaStream_t stream);

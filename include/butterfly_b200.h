@@ -149,6 +149,15 @@ int bfly_k_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, con
 int bfly_k_attn_decode(const void* q_bf16, const void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
                        int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int S, int T, int nq,
                        float* part_o, float* part_ml, int n_splits, void* out_bf16, void* stream);
+/* Decode step (one new token per sequence) as the engine runs it: RoPE + KV append + attention in ONE kernel.  qkv
+ * holds the QKV projection's fp32 split-K slices [n_partials][T][(nq + 2 kv_local) * head_dim] (q | k | v columns,
+ * partial_stride floats apart); the kernel folds them (+bias), rotates q and k (rope_table float2 [pos][head_dim/2],
+ * NULL = no rotation), appends the new K/V row of sequence t at position seq_lens[t] to the cache, and attends
+ * over seq_lens[t] + 1 positions.  Same result as bfly_k_rope_kv followed by bfly_k_attn_decode with S = 1. */
+int bfly_k_attn_decode_rope(const float* qkv, int n_partials, int64_t partial_stride, const void* bias_bf16,
+                            const float* rope_table, void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
+                            int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int T, int nq, float* part_o,
+                            float* part_ml, int n_splits, void* out_bf16, void* stream);
 /* The context split the engine uses for a decode forward of T rows (0 on bad arguments): callers of
  * bfly_k_attn_decode size part_o = T*nq*n_splits*head_dim and part_ml = T*nq*n_splits*2 floats from it.
  * S > 1 is allowed (token s of sequence b attends to seq_lens[b] + s + 1 cached positions); seq_lens and

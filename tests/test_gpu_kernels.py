@@ -257,6 +257,69 @@ def test_attn_decode(lib, cuda, d, nq, nk, ctx_lens, n_splits):
         bf16_close(out[b], want.reshape(-1), extra_abs=ATTN_ATOL)
 
 
+@pytest.mark.parametrize("d,nq,nk,ctx_lens,n_splits,n_part,theta,use_bias", [
+    (128, 4, 1, [1, 33, 257], 1, 3, 5e5, False), (128, 8, 2, [100, 5, 64], 4, 16, 5e5, False),
+    (128, 8, 1, [300, 17, 96, 32], 3, 1, 1e6, False), (64, 6, 6, [40, 41, 2], 2, 5, 0.0, True),
+    (32, 8, 4, [70, 1, 128], 5, 2, 1e4, True)])
+def test_attn_decode_with_fused_rope(lib, cuda, d, nq, nk, ctx_lens, n_splits, n_part, theta, use_bias):
+    """bfly_k_attn_decode_rope (RoPE + KV append + attention in one kernel, the engine's decode path) gives the
+    same bits as bfly_k_rope_kv followed by bfly_k_attn_decode, writes the same cache, and matches the oracle."""
+    B, ps = len(ctx_lens), 32
+    pps = (max(ctx_lens) + ps - 1) // ps
+    ld = (nq + 2 * nk) * d
+    g = torch.Generator().manual_seed(17)
+    perm = torch.randperm(B * pps, generator=g).to(torch.int32).reshape(B, pps)
+    kl, vl = gen((B * pps, nk, ps, d), 8, 1.0, torch.bfloat16), gen((B * pps, nk, ps, d), 10, 1.0, torch.bfloat16)
+    parts = gen((n_part, B, ld), 3, 0.5)
+    bias = gen((ld,), 4, 0.1, torch.bfloat16)
+    lens = torch.tensor([c - 1 for c in ctx_lens], dtype=torch.int32)        # tokens cached before the new one
+    max_pos = max(ctx_lens)
+    half = d // 2
+    inv = torch.pow(torch.tensor(theta if theta > 0 else 1.0, dtype=torch.float64), -2.0 * torch.arange(half, dtype=torch.float64) / d)
+    ang = torch.arange(max_pos, dtype=torch.float64)[:, None] * inv[None, :]
+    table = torch.stack([torch.cos(ang), torch.sin(ang)], dim=-1).float().contiguous()       # [pos][half][2]
+    d_parts, d_bias, d_table, d_perm, d_lens = parts.to(cuda), bias.to(cuda), table.to(cuda), perm.to(cuda), lens.to(cuda)
+    rope_ptr = d_table.data_ptr() if theta > 0 else None
+    bias_ptr = d_bias.data_ptr() if use_bias else None
+    slots = B * nq * n_splits
+
+    def scratch():
+        return (torch.zeros((slots * d,), dtype=torch.float32, device=cuda), torch.zeros((slots * 2,), dtype=torch.float32, device=cuda))
+
+    # reference path: two kernels
+    pages_a = pack_pages(kl, vl).to(cuda)
+    q_a = torch.zeros((B, nq * d), dtype=torch.bfloat16, device=cuda)
+    out_a = torch.zeros((B, nq * d), dtype=torch.bfloat16, device=cuda)
+    po, pml = scratch()
+    ok(lib, lib.bfly_k_rope_kv(d_parts.data_ptr(), n_part, B * ld, bias_ptr, rope_ptr, d_lens.data_ptr(), 1, B, nq, nk, d,
+                               q_a.data_ptr(), pages_a.data_ptr(), d_perm.data_ptr(), pps, ps, stream()))
+    ok(lib, lib.bfly_k_attn_decode(q_a.data_ptr(), pages_a.data_ptr(), d_perm.data_ptr(), pps, ps, nk, d, d_lens.data_ptr(), 1, B,
+                                   nq, po.data_ptr(), pml.data_ptr(), n_splits, out_a.data_ptr(), stream()))
+    # fused path
+    pages_b = pack_pages(kl, vl).to(cuda)
+    out_b = torch.zeros((B, nq * d), dtype=torch.bfloat16, device=cuda)
+    po, pml = scratch()
+    ok(lib, lib.bfly_k_attn_decode_rope(d_parts.data_ptr(), n_part, B * ld, bias_ptr, rope_ptr, pages_b.data_ptr(),
+                                        d_perm.data_ptr(), pps, ps, nk, d, d_lens.data_ptr(), B, nq, po.data_ptr(),
+                                        pml.data_ptr(), n_splits, out_b.data_ptr(), stream()))
+    assert torch.equal(pages_a.view(torch.int16), pages_b.view(torch.int16)), "fused kernel appended other K/V bits"
+    assert torch.equal(out_a.view(torch.int16), out_b.view(torch.int16)), "fused kernel differs from rope_kv + attn_decode"
+    # oracle: fold, bias, rope, append, attend
+    x = parts.sum(0) + (bias.float() if use_bias else 0.0)
+    qo = x[:, :nq * d].reshape(B, nq, d)
+    ko = x[:, nq * d:(nq + nk) * d].reshape(B, nk, d)
+    vo = x[:, (nq + nk) * d:].reshape(B, nk, d)
+    if theta > 0:
+        qo, ko = ops.rope(qo, lens.long(), theta), ops.rope(ko, lens.long(), theta)
+    for b, ctx in enumerate(ctx_lens):
+        pos = torch.arange(ctx)
+        pg = perm[b, pos // ps].long()
+        kk, vv = kl[pg, :, pos % ps, :].float().clone(), vl[pg, :, pos % ps, :].float().clone()   # [ctx, nk, d]
+        kk[ctx - 1], vv[ctx - 1] = ko[b].to(torch.bfloat16).float(), vo[b].to(torch.bfloat16).float()
+        want = ops.attention(qo[b].to(torch.bfloat16).float().reshape(1, 1, nq, d), kk[None], vv[None], ctx - 1)
+        bf16_close(out_b[b], want.reshape(-1), extra_abs=ATTN_ATOL)
+
+
 def test_attn_prefill_rows(lib, cuda):
     """S new tokens per sequence: token s of sequence b sees lens[b] + s + 1 keys (causal)."""
     d, nq, nk, ps, S = 64, 4, 2, 32, 5
