@@ -57,7 +57,7 @@ int launch_embed(const int* tokens, const bf16* table, const bf16* pos_table, co
 __global__ void __launch_bounds__(1024) add_norm_kernel(
     float* __restrict__ residual, const float* __restrict__ partials, int n_partials, int64_t partial_stride,
     const bf16* __restrict__ bias, const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float eps,
-    int layer_norm, bf16* __restrict__ out, int h) {
+    int layer_norm, bf16* __restrict__ out, int h, const bf16* __restrict__ partial_bf16) {
   pdl_trigger();
   pdl_wait();
   extern __shared__ __align__(16) float srow[];
@@ -67,6 +67,10 @@ __global__ void __launch_bounds__(1024) add_norm_kernel(
   float sum = 0.f, sumsq = 0.f;
   for (int i = threadIdx.x * 4; i < h; i += blockDim.x * 4) {
     float4 v = *reinterpret_cast<const float4*>(res + i);
+    if (partial_bf16 != nullptr) {                // one complete bf16 partial (prefill: all-reduced over the ranks)
+      const uint2 pb = *reinterpret_cast<const uint2*>(partial_bf16 + (int64_t)row * h + i);
+      v.x += bf16_lo(pb.x); v.y += bf16_hi(pb.x); v.z += bf16_lo(pb.y); v.w += bf16_hi(pb.y);
+    }
     const float* pp = partials + (int64_t)row * h + i;
     // slices are folded in index order, four loads in flight at a time (latency, not bandwidth, bound)
     int p = 0;
@@ -86,7 +90,7 @@ __global__ void __launch_bounds__(1024) add_norm_kernel(
       const uint2 b = *reinterpret_cast<const uint2*>(bias + i);
       v.x += bf16_lo(b.x); v.y += bf16_hi(b.x); v.z += bf16_lo(b.y); v.w += bf16_hi(b.y);
     }
-    if (n_partials > 0 || bias != nullptr) *reinterpret_cast<float4*>(res + i) = v;
+    if (n_partials > 0 || bias != nullptr || partial_bf16 != nullptr) *reinterpret_cast<float4*>(res + i) = v;
     *reinterpret_cast<float4*>(srow + i) = v;
     sum += (v.x + v.y) + (v.z + v.w);
     sumsq += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
@@ -121,7 +125,7 @@ __global__ void __launch_bounds__(1024) add_norm_kernel(
 
 int launch_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
                     const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
-                    int T, int h, cudaStream_t stream) {
+                    int T, int h, cudaStream_t stream, const bf16* partial_bf16) {
   BFLY_CHECK(T > 0 && h % 4 == 0 && h * 4 <= 160 * 1024, "add_norm: T>0, h%4==0, h<=40960");
   BFLY_CHECK(n_partials == 0 || partials != nullptr, "add_norm: partials missing");
   const size_t smem = (size_t)h * sizeof(float);
@@ -134,7 +138,7 @@ int launch_add_norm(float* residual, const float* partials, int n_partials, int6
   // rows in flight per SM
   const int threads = T >= 512 ? 256 : std::min(1024, std::max(128, ((h / 4 + 31) / 32) * 32));
   BFLY_CUDA(launch_pdl(add_norm_kernel, dim3(T), dim3(threads), smem, stream, residual, partials, n_partials, partial_stride, bias, gamma, beta,
-                                            eps, layer_norm, out, h));
+                                            eps, layer_norm, out, h, partial_bf16));
   count_launch();
   BFLY_CUDA(cudaGetLastError());
   return BFLY_OK;
@@ -625,6 +629,31 @@ __global__ void reduce_partials_kernel(const float* __restrict__ partials, int n
     v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
   }
   reinterpret_cast<float4*>(out)[i] = v;
+}
+
+// same fold, rounded once to bf16 (the payload of the prefill all-reduce at tp > 1)
+__global__ void reduce_partials_bf16_kernel(const float* __restrict__ partials, int n_partials, int64_t partial_stride,
+                                            bf16* __restrict__ out, int64_t count4) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= count4) return;
+  float4 v = reinterpret_cast<const float4*>(partials)[i];
+  for (int p = 1; p < n_partials; ++p) {
+    const float4 a = reinterpret_cast<const float4*>(partials + p * partial_stride)[i];
+    v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+  }
+  reinterpret_cast<uint2*>(out)[i] = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+}
+
+int launch_reduce_partials_bf16(const float* partials, int n_partials, int64_t partial_stride, bf16* out, int64_t count,
+                                cudaStream_t stream) {
+  BFLY_CHECK(count > 0 && count % 4 == 0 && n_partials >= 1 && partial_stride % 4 == 0, "reduce_partials_bf16: bad shape");
+  const int64_t c4 = count / 4;
+  BFLY_CUDA(launch_pdl(reduce_partials_bf16_kernel, dim3((unsigned)ceil_div64(c4, 256)), dim3(256), 0, stream, partials,
+                       n_partials, partial_stride, out, c4));
+  count_launch();
+  return BFLY_OK;
 }
 
 int launch_reduce_partials(const float* partials, int n_partials, int64_t partial_stride, float* out,

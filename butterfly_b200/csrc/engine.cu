@@ -58,7 +58,7 @@ int load_nccl() {
 }
 
 // ncclDataType_t / ncclRedOp_t values (nccl.h): ncclInt8 = 0, ncclFloat32 = 7, ncclSum = 0
-constexpr int kNcclInt8 = 0, kNcclFloat = 7, kNcclSum = 0;
+constexpr int kNcclInt8 = 0, kNcclFloat = 7, kNcclBfloat16 = 9, kNcclSum = 0;
 
 #define BFLY_NCCL(expr)                                                                          \
   do {                                                                                           \
@@ -146,6 +146,8 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     // 1.70): the fold sits on the attention kernel's critical path instead of overlapping its KV prefetch.  Opt-in.
     env = getenv("BFLY_FUSED_ROPE");
     e->fused_rope = env && env[0] == '1';
+    env = getenv("BFLY_PREFILL_AR_BF16");               // A/B knob; default on
+    e->prefill_ar_bf16 = !(env && env[0] == '0');
     env = getenv("BFLY_AR_CLUSTER");                    // A/B knob: 0 = one CTA per row (round-1 kernel)
     // (rows split over a cluster of CTAs measured SLOWER than one CTA per row at tp=2 and tp=8 -- more flags in
     //  flight, cluster launch cost -- so it is off unless asked for: "a" = automatic chunk count, "1".."8" = that many)
@@ -201,6 +203,7 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
   A(dev_alloc(e, &e->part_o, po, wsb));
   A(dev_alloc(e, &e->part_ml, pml, wsb));
   if (c.tp > 1) A(dev_alloc(e, &e->red, (size_t)maxT * h, wsb));
+  if (c.tp > 1) A(dev_alloc(e, &e->red_bf, (size_t)maxT * h, wsb));
   if (c.n_experts) A(dev_alloc(e, &e->route_w, (size_t)maxT * e->experts_local, wsb));
   if (c.n_experts && e->moe_grouped && maxT >= kMoeGroupedMinTokens) {
     e->moe_rows_cap = maxT * std::min(c.top_k, e->experts_local);
@@ -430,6 +433,14 @@ int Engine::all_reduce_f32(float* buf, size_t count) {
   return BFLY_OK;
 }
 
+int Engine::all_reduce_bf16(bf16* buf, size_t count) {
+  if (d.tp == 1) return BFLY_OK;
+  if (!comm && skip_collectives()) return BFLY_OK;
+  if (!comm) { set_error("tp > 1 but bfly_comm_init was not called"); return BFLY_ESTATE; }
+  BFLY_NCCL(g_nccl.AllReduce(buf, buf, count, kNcclBfloat16, kNcclSum, comm, stream));
+  return BFLY_OK;
+}
+
 int Engine::all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank) {
   if (!comm && skip_collectives()) return BFLY_OK;
   if (!comm) { set_error("tp > 1 but bfly_comm_init was not called"); return BFLY_ESTATE; }
@@ -460,12 +471,21 @@ int Engine::gemm_swiglu(const bf16* W, const bf16* X, int N) {
 
 // Row-parallel output: fold slices and all-reduce when tp > 1; tells the consumer where to read.
 int Engine::row_parallel_finish(int T, int slices, bool allow_fused, float* partials, const float** src,
-                                int* n_partials, bool* fused) {
+                                int* n_partials, bool* fused, const bf16** src_bf16) {
   const int h = d.hidden;
   *fused = false;
+  *src_bf16 = nullptr;
   if (d.tp == 1) { *src = partials; *n_partials = slices; return BFLY_OK; }
   if (allow_fused && p2p_ready && T <= ar.max_rows) {      // decode: the consumer kernel does the all-reduce
     *src = partials; *n_partials = slices; *fused = true;
+    return BFLY_OK;
+  }
+  // Bandwidth regime (prefill): the rank's folded partial crosses NVLink as bf16 -- half the bytes of the fp32
+  // all-reduce that dominated prefill at tp = 8 -- and is added to the fp32 residual by the norm kernel.
+  if (prefill_ar_bf16 && T >= kPrefillBf16MinRows) {
+    BFLY_TRY(launch_reduce_partials_bf16(partials, slices, (int64_t)T * h, red_bf, (int64_t)T * h, stream));
+    BFLY_TRY(all_reduce_bf16(red_bf, (size_t)T * h));
+    *src = nullptr; *n_partials = 0; *src_bf16 = red_bf;
     return BFLY_OK;
   }
   float* buf = partials;
@@ -516,7 +536,7 @@ int Engine::moe_ffn_grouped(const bf16* w_in, const bf16* w_down, int T) {
 
 // residual += (all-reduced) row-parallel output + bias; xn = norm(residual)
 int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,
-                       const bf16* beta) {
+                       const bf16* beta, const bf16* src_bf16) {
   const int h = d.hidden;
   const int ln = d.family == BFLY_FAMILY_GPT2;
   if (fused) {
@@ -526,7 +546,7 @@ int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call,
     return launch_ar_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, ar, idx,
                               ar_step, 2 * d.n_layers, two_shot, ar_chunks, ar_bf16, ar_lamport, stream);
   }
-  return launch_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, stream);
+  return launch_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, stream, src_bf16);
 }
 
 int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_logits, bool record_history) {
@@ -544,11 +564,12 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
   bool pend_fused = false, any_fused = false;
   const bool allow_fused = (S == 1);
   const bf16* pend_bias = nullptr;
+  const bf16* pend_bf16 = nullptr;
   for (int l = 0; l < c.n_layers; ++l) {
     const LayerW& w = layers[l];
     KvLayout kv{kv_pages + (int64_t)l * layer_kv_elems, table, pages_per_seq, c.page_size, kv_local, dh};
     int s = 1;
-    BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, w.attn_norm_w, w.attn_norm_b));
+    BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, w.attn_norm_w, w.attn_norm_b, pend_bf16));
     BFLY_TRY(gemm(w.wqkv, xn, h, qkv_rows, T, h, &s));
     const bool fuse_rope = S == 1 && fused_rope;
     if (!fuse_rope)
@@ -571,9 +592,9 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
       BFLY_TRY(launch_attn_decode(q, kv, lens, S, T, q_local, part_o, part_ml, attn_splits, attn_out, stream));
     }
     BFLY_TRY(gemm(w.wo, attn_out, q_local * dh, h, T, q_local * dh, &s));
-    BFLY_TRY(row_parallel_finish(T, s, allow_fused, ws, &pend_src, &pend_n, &pend_fused));
+    BFLY_TRY(row_parallel_finish(T, s, allow_fused, ws, &pend_src, &pend_n, &pend_fused, &pend_bf16));
     any_fused |= pend_fused;
-    BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, w.bo, w.ffn_norm_w, w.ffn_norm_b));
+    BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, w.bo, w.ffn_norm_w, w.ffn_norm_b, pend_bf16));
     if (c.n_experts)
       BFLY_TRY(launch_moe_router(xn, w.router, T, h, c.n_experts, c.top_k, c.rank * experts_local, experts_local,
                                  route_w, stream));
@@ -594,11 +615,11 @@ int Engine::forward(const int* tokens_dev, int seq0, int nb, int S, bool want_lo
       }
       BFLY_TRY(gemm(w.w_down, act, ffn_act_cols, h, T, ffn_act_cols, &s));
     }
-    BFLY_TRY(row_parallel_finish(T, s, allow_fused, ffn_out, &pend_src, &pend_n, &pend_fused));
+    BFLY_TRY(row_parallel_finish(T, s, allow_fused, ffn_out, &pend_src, &pend_n, &pend_fused, &pend_bf16));
     any_fused |= pend_fused;
     pend_bias = w.b_down;
   }
-  BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, final_norm_w, final_norm_b));
+  BFLY_TRY(norm_after(T, pend_src, pend_n, pend_fused, &ar_call, pend_bias, final_norm_w, final_norm_b, pend_bf16));
   // LM head on the last position of each sequence (row pitch S*h picks rows b*S + S-1)
   int s = 1;
   if (v_local > 0) {

@@ -14,6 +14,7 @@ namespace bfly {
 constexpr int kMaxSplits = 16;           // split-K cap used by the planner inside the engine
 constexpr int kMaxGreedySteps = 4096;    // history rows kept for bfly_decode_greedy
 constexpr size_t kPinnedBytes = 1 << 20;
+constexpr int kPrefillBf16MinRows = 256;     // forwards of at least this many rows all-reduce their partial sums as bf16
 constexpr int kMoeGroupedMinTokens = 256;   // MoE forwards of at least this many rows gather tokens per expert
 
 struct NcclId { char bytes[128]; };      // layout of ncclUniqueId
@@ -75,7 +76,8 @@ struct Engine {
   int *page_table = nullptr, *seq_lens = nullptr, *step_counter = nullptr;
   float2* rope_table = nullptr;
   float *residual = nullptr, *ws = nullptr, *red = nullptr, *part_o = nullptr, *part_ml = nullptr, *route_w = nullptr;
-  bf16 *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr;
+  bf16 *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *red_bf = nullptr;
+  bool prefill_ar_bf16 = true;
   float *logits = nullptr, *logits_all = nullptr;
   unsigned long long *keys = nullptr, *keys_all = nullptr;
   int *tokens_in = nullptr, *cur_tokens = nullptr, *history = nullptr;
@@ -131,10 +133,11 @@ struct Engine {
   int gemm_swiglu(const bf16* W, const bf16* X, int N);
   int moe_ffn_grouped(const bf16* w_in, const bf16* w_down, int T);
   int row_parallel_finish(int T, int splits, bool allow_fused, float* partials, const float** src, int* n_partials,
-                          bool* fused);
+                          bool* fused, const bf16** src_bf16);
   int norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,
-                 const bf16* beta);
+                 const bf16* beta, const bf16* src_bf16 = nullptr);
   int all_reduce_f32(float* buf, size_t count);
+  int all_reduce_bf16(bf16* buf, size_t count);
   int all_gather_bytes(const void* src, void* dst, size_t bytes_per_rank);
   int forward(const int* tokens_dev, int seq0, int nb, int S, bool want_logits, bool record_history);
   int fetch_outputs(int seq0, int B, float* logits_host, int32_t* next_host);

@@ -48,9 +48,10 @@ int launch_fill_synth(bf16* dst, int64_t dst_pitch, uint64_t key, int64_t ncols_
 int launch_embed(const int* tokens, const bf16* table, const bf16* pos_table, const int* seq_lens, int S,
                  float* residual, int T, int h, int vocab, unsigned long long* argmax_keys, int n_keys,
                  int* history, const int* step_counter, cudaStream_t stream);
+// partial_bf16 (optional): one more complete partial [T][h] in bf16, added like a slice (prefill at tp > 1)
 int launch_add_norm(float* residual, const float* partials, int n_partials, int64_t partial_stride,
                     const bf16* bias, const bf16* gamma, const bf16* beta, float eps, int layer_norm, bf16* out,
-                    int T, int h, cudaStream_t stream);
+                    int T, int h, cudaStream_t stream, const bf16* partial_bf16 = nullptr);
 int launch_rope_kv(const float* qkv, int n_partials, int64_t partial_stride, const bf16* bias,
                    const float2* rope_table, const int* seq_lens, int S, int T, int nq, int nk, bf16* q_out,
                    KvLayout kv, cudaStream_t stream);
@@ -69,6 +70,8 @@ int launch_moe_router(const bf16* xn, const bf16* router, int T, int h, int n_ex
                       int first_local, int n_local, float* route_w, cudaStream_t stream);
 int launch_reduce_partials(const float* partials, int n_partials, int64_t partial_stride, float* out,
                            int64_t count, cudaStream_t stream);
+int launch_reduce_partials_bf16(const float* partials, int n_partials, int64_t partial_stride, bf16* out, int64_t count,
+                                cudaStream_t stream);
 
 // allreduce_norm.cu -- decode-time all-reduce over NVLink peer memory fused with residual add + norm
 constexpr int kMaxPeers = 8;

@@ -103,6 +103,11 @@ def test_tp2_llama3_8b_width(cuda, tmp_path):
     _run(LLAMA3_8B.with_layers(2), 2, B=4, S=40, steps=3, tmp_path=tmp_path, ar_modes=(AR_ONE_SHOT, AR_TWO_SHOT))
 
 
+def test_tp2_llama3_8b_width_long_prefill(cuda, tmp_path):
+    """320 prefill rows: the bandwidth-regime all-reduce (bf16 payload over NCCL) instead of the fp32 one."""
+    _run(LLAMA3_8B.with_layers(2), 2, B=4, S=80, steps=2, tmp_path=tmp_path)
+
+
 def test_tp2_gpt2_small_full(cuda, tmp_path):
     """BASELINE.json configs[0]: GPT-2 small (124M) TP=2 greedy decode vs the CPU fp32 oracle."""
     _run(GPT2_SMALL, 2, B=1, S=64, steps=32, tmp_path=tmp_path)
