@@ -146,8 +146,11 @@ int Engine::create(const bfly_model_desc& desc, int device, Engine** out) {
     // 1.70): the fold sits on the attention kernel's critical path instead of overlapping its KV prefetch.  Opt-in.
     env = getenv("BFLY_FUSED_ROPE");
     e->fused_rope = env && env[0] == '1';
-    env = getenv("BFLY_PREFILL_AR_BF16");               // A/B knob; default on
-    e->prefill_ar_bf16 = !(env && env[0] == '0');
+    // bf16 payload for the prefill all-reduce: +7 % prefill at tp=2, +15 % at tp=8 (152.6 k -> 175.9 k tok/s), but NCCL
+    // rounds the running sum to bf16 at every ring hop and the logit error at tp=8 rose to 6.75 % of sigma against the
+    // 7 % gate (5.5 % with fp32) -- too little margin for a result that depends on NCCL's algorithm choice.  Opt-in.
+    env = getenv("BFLY_PREFILL_AR_BF16");
+    e->prefill_ar_bf16 = env && env[0] == '1';
     env = getenv("BFLY_AR_CLUSTER");                    // A/B knob: 0 = one CTA per row (round-1 kernel)
     // (rows split over a cluster of CTAs measured SLOWER than one CTA per row at tp=2 and tp=8 -- more flags in
     //  flight, cluster launch cost -- so it is off unless asked for: "a" = automatic chunk count, "1".."8" = that many)

@@ -77,7 +77,7 @@ struct Engine {
   float2* rope_table = nullptr;
   float *residual = nullptr, *ws = nullptr, *red = nullptr, *part_o = nullptr, *part_ml = nullptr, *route_w = nullptr;
   bf16 *xn = nullptr, *q = nullptr, *attn_out = nullptr, *act = nullptr, *red_bf = nullptr;
-  bool prefill_ar_bf16 = true;
+  bool prefill_ar_bf16 = false;
   float *logits = nullptr, *logits_all = nullptr;
   unsigned long long *keys = nullptr, *keys_all = nullptr;
   int *tokens_in = nullptr, *cur_tokens = nullptr, *history = nullptr;
