@@ -537,6 +537,14 @@ int Engine::moe_ffn_grouped(const bf16* w_in, const bf16* w_down, int T) {
   return BFLY_OK;
 }
 
+// Size rule of the decode all-reduce (mode -1).  Measured with the flag-free protocol: at tp=8 two-shot wins even for
+// the 32 x 4096 rows of the 8B shape (isolated exchange 11.8 vs 13.3 us, decode step 2.13 vs 2.20 ms) because one-shot
+// moves tp x the bytes; at tp=2 one-shot wins (6.8 vs 8.4 us); tp=4 keeps the round-1 threshold of 1 MiB per call.
+int Engine::ar_two_shot_by_size(int T) const {
+  if (d.tp >= 8) return 1;
+  return d.tp >= 4 && (size_t)T * d.hidden * sizeof(float) >= (1u << 20);
+}
+
 // residual += (all-reduced) row-parallel output + bias; xn = norm(residual)
 int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call, const bf16* bias, const bf16* gamma,
                        const bf16* beta, const bf16* src_bf16) {
@@ -545,7 +553,7 @@ int Engine::norm_after(int T, const float* src, int n, bool fused, int* ar_call,
   if (fused) {
     const int idx = (*ar_call)++;
     // every rank takes the same branch: T, h, tp and the mode are identical across the group
-    const int two_shot = ar_mode >= 0 ? ar_mode : (d.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
+    const int two_shot = ar_mode >= 0 ? ar_mode : ar_two_shot_by_size(T);
     return launch_ar_add_norm(residual, src, n, (int64_t)T * h, bias, gamma, beta, d.norm_eps, ln, xn, T, h, ar, idx,
                               ar_step, 2 * d.n_layers, two_shot, ar_chunks, ar_bf16, ar_lamport, stream);
   }
@@ -951,7 +959,7 @@ int Engine::bench_allreduce(int T, int iters, float* us_allreduce, float* us_pla
   BFLY_CHECK(T >= 1 && T <= ar.max_rows && T <= d.max_tokens && iters >= 1 && us_allreduce && us_plain, "bench_allreduce: arguments");
   BFLY_CUDA(cudaSetDevice(device));
   const int h = d.hidden, calls = 2 * d.n_layers, ln = d.family == BFLY_FAMILY_GPT2;
-  const int two_shot = ar_mode >= 0 ? ar_mode : (d.tp >= 4 && (size_t)T * h * sizeof(float) >= (1u << 20));
+  const int two_shot = ar_mode >= 0 ? ar_mode : ar_two_shot_by_size(T);
   BFLY_CUDA(cudaMemsetAsync(ws, 0, (size_t)T * h * sizeof(float), stream));
   BFLY_CUDA(cudaMemsetAsync(residual, 0, (size_t)T * h * sizeof(float), stream));
   cudaEvent_t e0, e1;

@@ -117,6 +117,7 @@ struct Engine {
   int comm_init(const void* id128, int world, int rank);
   int set_page_table(const int32_t* table_host, int n_seqs, int pps);
   int set_ar_mode(int mode);
+  int ar_two_shot_by_size(int T) const;
   int bench_allreduce(int T, int iters, float* us_allreduce, float* us_plain);
 
   int prefill(const int32_t* tokens_host, int B, int S, float* logits_host, int32_t* next_host);

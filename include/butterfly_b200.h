@@ -86,8 +86,8 @@ int bfly_weights_ready(bfly_ctx* ctx);   /* validates names/shapes; required bef
 int bfly_comm_unique_id(void* out_id128);                       /* rank 0; 128 bytes */
 int bfly_comm_init(bfly_ctx* ctx, const void* id128, int world, int rank);
 
-/* Mode of the decode-time all-reduce over peer memory (tp > 1): -1 = chosen by size (two-shot when the
- * rows of one call total >= 1 MiB and tp >= 4), 0 = one-shot (every rank pushes its rows to every rank),
+/* Mode of the decode-time all-reduce over peer memory (tp > 1): -1 = chosen by size (two-shot at tp >= 8, and at
+ * tp >= 4 when the rows of one call total >= 1 MiB), 0 = one-shot (every rank pushes its rows to every rank),
  * 1 = two-shot (row r is reduced by rank r % tp and pushed back).  Both modes add in rank order, so results
  * are bit-identical.  Call it at a quiescent point with the SAME value on every rank. */
 int bfly_set_ar_mode(bfly_ctx* ctx, int mode);
