@@ -313,8 +313,7 @@ def parity_leg(dist, world, rank, local):
     from parity_gates import LOGIT_TOL, REL_MAX, REL_RMS, Gate
     from butterfly_b200 import LLAMA3_8B, LLAMA3_70B, Model, SyntheticSource, make_plan, shard_weights, synthetic_tokens
     import hashlib
-    # 4 x 64 = 256 prefill rows: the same bf16-payload NCCL all-reduce the timed prefill uses at tp > 1
-    cases = [("llama3-8b width, 2 layers, B=4, prefill 64 + 4 teacher-forced steps", LLAMA3_8B.with_layers(2), 4, 64, 4,
+    cases = [("llama3-8b width, 2 layers, B=4, prefill 48 + 4 teacher-forced steps", LLAMA3_8B.with_layers(2), 4, 48, 4,
               (0, 1) if world > 1 else (-1,))]
     if world >= 4:     # 64 x 8192 fp32 decode rows = 2 MiB per call: the size rule (-1) picks two-shot by itself
         cases.append(("llama3-70b width, 1 layer, B=64 (2 MiB per all-reduce), prefill 8 + 3 steps",
