@@ -635,6 +635,14 @@ GemmPlan gemm_plan(int M, int N, int K, int sm_count, int max_splits, int dual, 
   }
   const size_t stage_bytes = kABytes * (size_t)(1 + dual) + (size_t)(p.bn >> p.pair) * BK * 2;
   int stages = (p.bn <= 64) ? ((dual || p.cluster) ? 3 : 4) : (int)std::min<size_t>(kMaxStages, (200 * 1024) / stage_bytes);
+  // weight-streaming regime: a 5th stage where two CTAs still share an SM (token tiles <= 32: 2 x 104 KB) -- measured
+  // on the isolated kernel (tools/microbench/gemm_probe.py): gate/up 5822 -> 6035 GB/s, LM head 6274 -> 6395 GB/s
+  static const int small_stages = [] { const char* e = getenv("BFLY_GEMM_STAGES_SMALL"); return e ? atoi(e) : 0; }();
+  if (p.bn <= 64 && !dual && !p.cluster) {
+    int want = small_stages > 0 ? small_stages : 5;        // decode step: tp=1 4.744 -> 4.727 ms, tp=8 shard 1.762 -> 1.735 ms
+    if (2 * smem_needed(p.bn, want, dual, 0) > 227 * 1024) want = 4;
+    stages = want;
+  }
   static const int big_stages = [] { const char* e = getenv("BFLY_GEMM_STAGES_BIG"); return e ? atoi(e) : 0; }();
   if (p.bn > 64 && big_stages > 0) stages = big_stages;         // experiment knob: 3 lets two pair-CTAs share an SM
   stages = std::max(2, std::min(stages, kMaxStages));
