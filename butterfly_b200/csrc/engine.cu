@@ -962,9 +962,13 @@ int Engine::bench_allreduce(int T, int iters, float* us_allreduce, float* us_pla
   const int two_shot = ar_mode >= 0 ? ar_mode : ar_two_shot_by_size(T);
   BFLY_CUDA(cudaMemsetAsync(ws, 0, (size_t)T * h * sizeof(float), stream));
   BFLY_CUDA(cudaMemsetAsync(residual, 0, (size_t)T * h * sizeof(float), stream));
-  cudaEvent_t e0, e1;
-  BFLY_CUDA(cudaEventCreate(&e0));
-  BFLY_CUDA(cudaEventCreate(&e1));
+  struct Events {                               // destroyed on every return path
+    cudaEvent_t a = nullptr, b = nullptr;
+    ~Events() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+  } ev;
+  BFLY_CUDA(cudaEventCreate(&ev.a));
+  BFLY_CUDA(cudaEventCreate(&ev.b));
+  cudaEvent_t e0 = ev.a, e1 = ev.b;
   auto run = [&](int n, bool with_ar) -> int {
     for (int i = 0; i < n; ++i) {
       if (with_ar) {
@@ -994,8 +998,6 @@ int Engine::bench_allreduce(int T, int iters, float* us_allreduce, float* us_pla
   BFLY_CUDA(cudaStreamSynchronize(stream));
   BFLY_CUDA(cudaEventElapsedTime(&ms, e0, e1));
   *us_plain = ms * 1e3f / (float)n;
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   return BFLY_OK;
 }
 
@@ -1003,6 +1005,7 @@ int Engine::bench_allreduce(int T, int iters, float* us_allreduce, float* us_pla
 // step complete (entry 0 = kernel start); returns the number of entries, 0 when tracing is off.
 int Engine::read_step_trace(unsigned long long* out, int max_entries, int* n_out, int* splits_out) {
   *n_out = 0;
+  *splits_out = 0;
   for (auto& kv : step_plans) {
     const StepPlan& sp = kv.second;
     if (sp.p.trace == nullptr) continue;
