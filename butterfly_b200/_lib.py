@@ -63,6 +63,7 @@ SIGNATURES = {
     "bfly_k_rope_kv": (i32, [vp, i32, i64, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp]),
     "bfly_k_attn_decode": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, i32, vp, vp, i32, vp, vp]),
     "bfly_k_attn_decode_rope": (i32, [vp, i32, i64, vp, vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, vp, vp, i32, vp, vp]),
+    "bfly_k_step_gemm_table": (i32, [i32, i32, i32, vp, vp, C.POINTER(i32)]),
     "bfly_k_attn_decode_splits": (i32, [i32, i32, i32]),
     "bfly_k_attn_prefill": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, i32, vp, vp]),
     "bfly_k_attn_decode_static": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, i32, i32, vp, vp]),

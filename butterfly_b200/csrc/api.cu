@@ -280,6 +280,28 @@ int bfly_k_attn_decode_rope(const float* qkv, int n_partials, int64_t partial_st
   });
 }
 
+int bfly_k_step_gemm_table(int M, int K, int grid, uint16_t* first_out, uint8_t* nsl_out, int* max_slices) {
+  return guarded(nullptr, [&]() -> int {
+    BFLY_CHECK(M > 0 && K > 0 && grid > 0 && grid <= 65535 && first_out && nsl_out && max_slices, "step_gemm_table: arguments");
+    StepGemm g{};
+    g.M = M; g.K = K;
+    g.nkb = ceil_div(K, 64);
+    g.m_tiles = ceil_div(M, 128);
+    g.units = g.m_tiles * g.nkb;
+    g.ge = std::min(grid, g.units);
+    int mx = 1;
+    for (int t = 0; t < g.m_tiles; ++t) {
+      const int a = sk_owner(g, t * g.nkb), b = sk_owner(g, t * g.nkb + g.nkb - 1);
+      BFLY_CHECK(b - a + 1 <= 255, "step_gemm_table: more than 255 slices per tile");
+      first_out[t] = (uint16_t)a;
+      nsl_out[t] = (uint8_t)(b - a + 1);
+      mx = std::max(mx, b - a + 1);
+    }
+    *max_slices = mx;
+    return BFLY_OK;
+  });
+}
+
 int bfly_k_attn_decode_splits(int T, int kv_local, int max_ctx) {
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) {

@@ -158,6 +158,11 @@ int bfly_k_attn_decode_rope(const float* qkv, int n_partials, int64_t partial_st
                             const float* rope_table, void* kv_pages_bf16, const int32_t* page_table, int pages_per_seq,
                             int page_size, int kv_local, int head_dim, const int32_t* seq_lens, int T, int nq, float* part_o,
                             float* part_ml, int n_splits, void* out_bf16, void* stream);
+/* Host-only (no GPU needed): the stream-K partition the fused decode step kernel uses for a weight matrix [M][K] on
+ * `grid` CTAs -- first_out[t] = first CTA holding K blocks of 128-row tile t, nsl_out[t] = number of CTAs (= fp32 slices)
+ * tile t is spread over; both arrays have ceil(M/128) entries.  CTA c owns units [c*U/g, (c+1)*U/g) of the U =
+ * ceil(M/128)*ceil(K/64) (tile, K block) units in tile-major order, g = min(grid, U). */
+int bfly_k_step_gemm_table(int M, int K, int grid, uint16_t* first_out, uint8_t* nsl_out, int* max_slices);
 /* The context split the engine uses for a decode forward of T rows (0 on bad arguments): callers of
  * bfly_k_attn_decode size part_o = T*nq*n_splits*head_dim and part_ml = T*nq*n_splits*2 floats from it.
  * S > 1 is allowed (token s of sequence b attends to seq_lens[b] + s + 1 cached positions); seq_lens and
