@@ -121,16 +121,18 @@ class CpuDecode:
     layer applications cycle through `distinct` sets of weights and caches (4 sets = 3.5 GB of weights, far
     beyond any CPU cache), which leaves flops and bytes per step unchanged."""
 
-    def __init__(self, ctx: int = CTX, batch: int = BATCH):
+    def __init__(self, ctx: int = CTX, batch: int = BATCH, full=None, distinct=None):
+        """`full` (default: the Llama-3-8B shape) and `distinct` (default: by available host memory) exist so the CPU
+        suite can run this class on a tiny shape."""
         from butterfly_b200 import LLAMA3_8B, make_plan
         from butterfly_b200.weights import RankWeights, shard_spec
         from oracle import OracleModel
 
         self.cores = os.cpu_count() or 1
         torch.set_num_threads(self.cores)
-        full = LLAMA3_8B
+        full = full or LLAMA3_8B
         self.avail_gb = _mem_available_gb()
-        self.distinct = full.n_layers if self.avail_gb >= 80.0 else 4
+        self.distinct = distinct or (full.n_layers if self.avail_gb >= 80.0 else min(4, full.n_layers))
         cfg = full.with_layers(self.distinct)
         plan = make_plan(cfg, 1)
         g = torch.Generator().manual_seed(0)
